@@ -1,0 +1,252 @@
+/* interp_b200.h -- flat C ABI of the B200-native interplib hot path.
+ *
+ * One shared library (libinterp_b200.so, hand-written CUDA for sm_100a) sits exactly where the
+ * reference's CPython extension (the .c files of `src/python/`, L4 in SURVEY.md section 1) calls down into
+ * its table layer and runs its per-element loops.  Every entry point cites the reference
+ * interface it replaces (paths are into /root/reference).  Conventions:
+ *
+ *   - plain pointers and sizes only; all floating point is IEEE double; indices are unsigned /
+ *     size_t; the element index is always the slowest dimension, and inside one element the
+ *     reference's row-major layouts are kept verbatim (last index fastest,
+ *     `multidim_iterator_t` contract, e.g. src/python/mass_matrices.c:264-323);
+ *   - every function returns an `interp_result_t` value (same numbering as
+ *     src/common/error.h:9-25, extended with IB200_* codes); nothing aborts, no C++ exception
+ *     crosses the boundary; `ib200_last_error()` returns the text of the last failure;
+ *   - the caller owns every host buffer; the library owns device scratch and the device-side
+ *     table cache inside the context;
+ *   - batched calls take `where`: IB200_HOST  = pointers are host memory, the call stages
+ *     chunks through pinned buffers (H2D -> kernels -> D2H) and returns when `out` is
+ *     complete; IB200_DEVICE = pointers are device memory on the context's device, work is
+ *     queued on the context stream and the call returns immediately.
+ *   - there is NO CPU fallback for the batched hot path: without a CUDA device the context
+ *     cannot be created and the batched calls fail with IB200_ERROR_NO_DEVICE.
+ */
+#ifndef INTERP_B200_H
+#define INTERP_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define IB200_API __attribute__((visibility("default")))
+#else
+#define IB200_API
+#endif
+
+/* ---- A14: POD descriptors, numbering identical to the reference ------------------------ */
+
+/* src/common/error.h:9-25 */
+typedef enum
+{
+    INTERP_SUCCESS = 0,
+    INTERP_ERROR_NOT_IN_DOMAIN,
+    INTERP_ERROR_NOT_INCREASING,
+    INTERP_ERROR_FAILED_ALLOCATION,
+    INTERP_ERROR_BAD_SYSTEM,
+    INTERP_ERROR_INVALID_ENUM,
+    INTERP_ERROR_NOT_IN_REGISTRY,
+    INTERP_ERROR_GEOID_OUT_OF_RANGE,
+    INTERP_ERROR_GEOID_NOT_VALID,
+    INTERP_ERROR_SURFACE_NOT_CLOSED,
+    INTERP_ERROR_OBJECT_CONNECTED_TWICE,
+    INTERP_ERROR_MATRIX_DIMS_MISMATCH,
+    INTERP_ERROR_COUNT,
+    /* extensions of this library */
+    IB200_ERROR_CUDA = 100,        /* a CUDA runtime call or kernel failed               */
+    IB200_ERROR_NO_DEVICE = 101,   /* no usable sm_100 device / context not created      */
+    IB200_ERROR_BAD_ARGUMENT = 102,/* NULL pointer, dimension or index out of range      */
+    IB200_ERROR_UNSUPPORTED = 103, /* valid request outside the implemented envelope     */
+} interp_result_t;
+
+/* src/basis/basis_set.h:11-20 */
+typedef enum
+{
+    BASIS_INVALID = 0,
+    BASIS_LEGENDRE,
+    BASIS_LAGRANGE_GAUSS_LOBATTO,
+    BASIS_LAGRANGE_GAUSS,
+    BASIS_LAGRANGE_UNIFORM,
+    BASIS_LAGRANGE_CHEBYSHEV_GAUSS,
+    BASIS_BERNSTEIN,
+} basis_set_type_t;
+
+/* src/integration/integration_rules.h:7-12 */
+typedef enum
+{
+    INTEGRATION_RULE_TYPE_NONE = 0,
+    INTEGRATION_RULE_TYPE_GAUSS_LEGENDRE,
+    INTEGRATION_RULE_TYPE_GAUSS_LOBATTO,
+} integration_rule_type_t;
+
+/* src/basis/basis_set.h:22-26 */
+typedef struct
+{
+    basis_set_type_t type;
+    unsigned order;
+} basis_spec_t;
+
+/* src/integration/integration_rules.h:17-21 */
+typedef struct
+{
+    integration_rule_type_t type;
+    unsigned order;
+} integration_spec_t;
+
+enum
+{
+    IB200_MAX_DIM = 3,   /* reference dimensions supported by the batched kernels          */
+    IB200_MAX_PHYS = 3,  /* physical coordinates per point                                 */
+    IB200_HOST = 0,
+    IB200_DEVICE = 1,
+};
+
+/* src/common/error.c:9-38 (interp_error_str / interp_error_msg) + the IB200_* codes */
+IB200_API const char *ib200_error_str(int code);
+IB200_API const char *ib200_error_msg(int code);
+/* text of the last failure on the calling thread ("" if none) */
+IB200_API const char *ib200_last_error(void);
+IB200_API const char *ib200_version(void);
+
+/* ---- A1-A4, A10, A11: host-side 1-D tables (bit-exact restatements, no GPU needed) ------ */
+
+/* integration_rule_for_order, src/integration/integration_rules.c:40-73: nodes[order+1]
+ * ascending, weights[order+1]; accuracy may be NULL.  Gauss-Legendre:
+ * src/integration/gauss_legendre.c:7-50, Gauss-Lobatto: src/integration/gauss_lobatto.c:14-61
+ * (tol 1e-14, 1000 iterations). */
+IB200_API int ib200_rule_1d(integration_spec_t spec, double *nodes, double *weights, unsigned *accuracy);
+/* integration_rule_for_accuracy, src/integration/integration_rules.c:15-39 */
+IB200_API int ib200_rule_order_for_accuracy(integration_rule_type_t type, unsigned accuracy, unsigned *order);
+/* generate_lagrange_roots, src/basis/basis_lagrange.c:11-42 (tol 1e-12, 100 iterations) */
+IB200_API int ib200_lagrange_roots(basis_spec_t spec, double *roots);
+/* basis_set_t payload, src/basis/basis_set.h:28-55 as filled by lagrange_basis_create
+ * (src/basis/basis_lagrange.c:45-71), legendre_basis_create (src/basis/basis_legendre.c:9-40),
+ * bernstein_basis_create (src/basis/basis_bernstein.c:9-23): values[n][m] and
+ * derivatives[n][m], basis-major, n = basis order+1, m = rule order+1. */
+IB200_API int ib200_basis_table_1d(basis_spec_t basis, integration_spec_t rule, double *values, double *derivatives);
+/* integration_space_weights / _nodes, src/python/integration_objects.c:633-716, 731-814:
+ * weights[Q] (product built in ascending dimension order), nodes[d][Q]. */
+IB200_API int ib200_integration_space_weights(unsigned ndim, const integration_spec_t *rules, double *weights);
+IB200_API int ib200_integration_space_nodes(unsigned ndim, const integration_spec_t *rules, double *nodes);
+/* function_space_values_at_integration_nodes, src/python/function_space_objects.c:301-474:
+ * out[Q][N] = prod_dim B_dim[i_dim][q_dim]. */
+IB200_API int ib200_values_at_integration_nodes(unsigned ndim, const basis_spec_t *basis,
+                                                const integration_spec_t *rules, double *out);
+/* basis_compute_at_point_values / _derivatives, src/basis/basis_set.c:462-556 (BasisSpecs.values /
+ * .derivatives, src/python/basis_objects.c:351-491): out[cnt][n] at arbitrary points. */
+IB200_API int ib200_basis_at_points(basis_spec_t basis, size_t cnt, const double *x, double *values,
+                                    double *derivatives);
+/* basis_compute_outer_product_basis, src/basis/basis_set.c:577-633 (FunctionSpace.evaluate,
+ * src/python/function_space_objects.c:142-276): out[cnt][N]; x[k] points to cnt coordinates. */
+IB200_API int ib200_function_space_evaluate(unsigned ndim, const basis_spec_t *basis, size_t cnt,
+                                            const double *const *x, double *out);
+
+/* ---- context ---------------------------------------------------------------------------- */
+
+typedef struct ib200_ctx ib200_ctx_t;
+
+IB200_API int ib200_device_count(int *count);
+/* One context per GPU per process: owns a stream, pinned staging buffers, the device table
+ * cache keyed like the reference registries (basis type, order, rule type, rule order;
+ * src/basis/basis_set.c:212-287) and scratch.  Thread-safe (internal mutex). */
+IB200_API int ib200_ctx_create(int device, ib200_ctx_t **out);
+IB200_API int ib200_ctx_destroy(ib200_ctx_t *ctx);
+IB200_API int ib200_ctx_synchronize(ib200_ctx_t *ctx);
+/* adopt an external cudaStream_t (e.g. torch's current stream); NULL restores the own stream */
+IB200_API int ib200_ctx_set_stream(ib200_ctx_t *ctx, void *cuda_stream);
+/* name[len] = device name; sm_count, cc = major*10+minor, total device bytes (each may be NULL) */
+IB200_API int ib200_ctx_info(ib200_ctx_t *ctx, char *name, size_t len, int *sm_count, int *cc, size_t *mem_bytes);
+/* number of kernel launches / entries in the device table cache since creation (IntegrationRegistry.usage()
+ * analogue, src/python/integration_objects.c:90-149) */
+IB200_API int ib200_ctx_stats(ib200_ctx_t *ctx, unsigned long long *kernel_launches, unsigned *cached_tables);
+IB200_API int ib200_ctx_clear_cache(ib200_ctx_t *ctx);
+/* force the generic (any-dimension, any-order) kernels instead of the specialised ones: testing aid */
+IB200_API int ib200_ctx_set_force_generic(ib200_ctx_t *ctx, int on);
+/* host-pointer calls: elements per staged chunk (0 = automatic) */
+IB200_API int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements);
+
+/* device / pinned memory and stream-ordered copies for callers that keep results resident */
+IB200_API int ib200_device_alloc(ib200_ctx_t *ctx, size_t bytes, void **dptr);
+IB200_API int ib200_device_free(ib200_ctx_t *ctx, void *dptr);
+IB200_API int ib200_pinned_alloc(ib200_ctx_t *ctx, size_t bytes, void **hptr);
+IB200_API int ib200_pinned_free(ib200_ctx_t *ctx, void *hptr);
+IB200_API int ib200_copy_h2d(ib200_ctx_t *ctx, void *dst_dev, const void *src_host, size_t bytes);
+IB200_API int ib200_copy_d2h(ib200_ctx_t *ctx, void *dst_host, const void *src_dev, size_t bytes);
+IB200_API int ib200_device_memset(ib200_ctx_t *ctx, void *dptr, int byte, size_t bytes);
+/* CUDA-event stopwatch on the context stream (slot 0..7): start, stop, elapsed (syncs on stop event) */
+IB200_API int ib200_timer_start(ib200_ctx_t *ctx, unsigned slot);
+IB200_API int ib200_timer_stop(ib200_ctx_t *ctx, unsigned slot);
+IB200_API int ib200_timer_elapsed_ms(ib200_ctx_t *ctx, unsigned slot, float *ms);
+
+/* ---- A5/A6 (K1): batched reconstruction at integration points ---------------------------- */
+/* compute_integration_point_values[_derivatives], src/python/degrees_of_freedom.c:232-303
+ * (entries :426-510, :622-722).  For element e and field f:
+ *   out[e][f][q] = sum_i ( prod_dim T_dim[i_dim][q_dim] ) * dofs[e][i],
+ *   T_dim = D (derivative table) if bit `dim` of deriv_masks[f] is set, else B.
+ * deriv_masks = {0} is reconstruct_at_integration_points, {1<<k} the derivative along k;
+ * {0, 1, 2} is the 2-D "basis + gradient" evaluation (u, du/dxi0, du/dxi1) in one pass.
+ * dofs[E][N], out[E][n_fields][Q]. */
+IB200_API int ib200_reconstruct_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                      const integration_spec_t *rules, size_t n_elements, const double *dofs,
+                                      unsigned n_fields, const unsigned *deriv_masks, double *out, int where);
+
+/* ---- A9 (K0): batched element geometry ---------------------------------------------------- */
+/* coordinate_map_new + space_map_new, src/python/mappings.c:8-90, 304-556 with
+ * matrix_qr_decompose / matrix_back_substitute (src/operations/matrices.c:15-86, 117-141).
+ * geom_dofs[E][n_phys][N_g] are the coordinate DoFs in the space `geom_basis`.
+ * Outputs (each may be NULL): coords[E][n_phys][1+ndim][Q]  (CoordinateMap storage: values then
+ * the ndim reference gradients, src/python/mappings.h:6-12), det[E][Q] (= prod diag(R), the Gram
+ * determinant when n_phys > ndim), jinv[E][Q][ndim][n_phys] (left inverse). */
+IB200_API int ib200_geometry_batch(ib200_ctx_t *ctx, unsigned ndim, unsigned n_phys, const basis_spec_t *geom_basis,
+                                   const integration_spec_t *rules, size_t n_elements, const double *geom_dofs,
+                                   double *coords, double *det, double *jinv, int where);
+
+/* ---- A7/A8 (K2): batched element mass matrices --------------------------------------------- */
+/* compute_mass_matrix, src/python/mass_matrices.c:161-339 and compute_gradient_mass_matrix,
+ * :341-565.  out[E][N_out][N_in]:
+ *   out[e][j][i] = sum_q weight[e][q] * W[q] * phi_in_i(q) * phi_out_j(q)
+ * W = tensor rule weights; `weight` is NULL (reference-domain integration, IntegrationSpace
+ * branch) or the per-point factor [E][Q] (det for the SpaceMap branch of A7, det*Jinv[idx_in][idx_out]
+ * for A8).  deriv_dim_in >= 0 replaces the input basis by its derivative along that dimension (A8),
+ * -1 = plain mass matrix.  When the two spaces match (function_spaces_match, :142-159) only the
+ * lower triangle is integrated and mirrored exactly, like the reference (:326-335, :551-560 --
+ * the reference mirrors the gradient matrix too; reproduced). */
+IB200_API int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
+                                      const basis_spec_t *basis_out, const integration_spec_t *rules,
+                                      size_t n_elements, const double *weight, int deriv_dim_in, double *out,
+                                      int where);
+/* Same with the geometry prologue fused (K0 + K2): the SpaceMap is never materialised.
+ * idx_in < 0: mass matrix weighted by det (A7 with a SpaceMap); idx_in >= 0: gradient mass matrix
+ * with weight det*Jinv[idx_in][idx_out] (A8 with a SpaceMap). */
+IB200_API int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
+                                             const basis_spec_t *basis_out, const integration_spec_t *rules,
+                                             unsigned n_phys, const basis_spec_t *geom_basis, size_t n_elements,
+                                             const double *geom_dofs, int idx_in, int idx_out, double *out,
+                                             int where);
+
+/* ---- A12 (K3): batched L2-projection right-hand sides -------------------------------------- */
+/* projection_l2_dual, python/interplib/integration.py:106-168 (+ _prepare_integration :44-67):
+ *   out[e][i] = sum_q fvals[e][q] * W[q] * det[e][q] * Phi[q][i]
+ * fvals[E][Q] = the callable sampled at the (mapped) integration nodes; det may be NULL. */
+IB200_API int ib200_l2_dual_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                  const integration_spec_t *rules, size_t n_elements, const double *fvals,
+                                  const double *det, double *out, int where);
+/* geometry fused: det computed from geom_dofs in the same kernel */
+IB200_API int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                         const integration_spec_t *rules, unsigned n_phys,
+                                         const basis_spec_t *geom_basis, size_t n_elements,
+                                         const double *geom_dofs, const double *fvals, double *out, int where);
+
+/* ---- N1 ("next"): batched primal solve M u = b --------------------------------- */
+/* projection_l2_primal, python/interplib/integration.py:171-223 (np.linalg.solve per element).
+ * mass[E][N][N] symmetric positive definite (destroyed: overwritten by its Cholesky factor),
+ * rhs[E][N] overwritten by the solution. */
+IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
+                                    int where);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INTERP_B200_H */
