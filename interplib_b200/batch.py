@@ -1,0 +1,337 @@
+"""Element-batched front-end of the C ABI: NumPy arrays in, NumPy arrays out, the GPU in between.
+
+The reference has no batched API (one element per Python call); these functions
+are the batched counterparts of its per-element entry points and call straight into
+``libinterp_b200.so`` with host pointers.  ``Context.device_*`` variants keep data resident on the GPU.
+
+Specs are plain tuples: a function space is ``[(basis_type, order), ...]`` (one entry per reference
+dimension, names as in ``interplib.BasisType``) and an integration space is ``[(method, order), ...]``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+
+import numpy as np
+
+from . import _lib
+from ._lib import DEVICE, HOST, basis_specs, check, lib, rule_specs
+
+
+def _n_basis(basis) -> int:
+    return int(np.prod([int(o) + 1 for _, o in basis], dtype=np.int64))
+
+
+def _n_points(rules) -> int:
+    return int(np.prod([int(o) + 1 for _, o in rules], dtype=np.int64))
+
+
+def _as_in(a, shape) -> np.ndarray:
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a.reshape(shape)
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))  # raw device / pinned address
+
+
+class DeviceBuffer:
+    """A device allocation owned by a :class:`Context` (``ib200_device_alloc``)."""
+
+    def __init__(self, ctx: "Context", nbytes: int):
+        self.ctx = ctx
+        self.nbytes = int(nbytes)
+        p = C.c_void_p()
+        check(lib.ib200_device_alloc(ctx.handle, self.nbytes, C.byref(p)))
+        self.ptr = p.value
+
+    def upload(self, host: np.ndarray) -> "DeviceBuffer":
+        host = np.ascontiguousarray(host)
+        assert host.nbytes <= self.nbytes
+        check(lib.ib200_copy_h2d(self.ctx.handle, self.ptr, host.ctypes.data_as(C.c_void_p), host.nbytes))
+        return self
+
+    def download(self, shape, dtype=np.float64, offset_bytes: int = 0) -> np.ndarray:
+        out = np.empty(shape, dtype=dtype)
+        assert offset_bytes + out.nbytes <= self.nbytes
+        check(lib.ib200_copy_d2h(self.ctx.handle, out.ctypes.data_as(C.c_void_p), self.ptr + offset_bytes, out.nbytes))
+        return out
+
+    def free(self) -> None:
+        if self.ptr:
+            check(lib.ib200_device_free(self.ctx.handle, self.ptr))
+            self.ptr = None
+
+    def __int__(self) -> int:
+        return int(self.ptr)
+
+
+class PinnedArray:
+    """Page-locked host memory viewed as a NumPy array (``ib200_pinned_alloc``)."""
+
+    def __init__(self, ctx: "Context", shape, dtype=np.float64):
+        self.ctx = ctx
+        n = int(np.prod(shape, dtype=np.int64)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        check(lib.ib200_pinned_alloc(ctx.handle, n, C.byref(p)))
+        self.ptr = p.value
+        buf = (C.c_char * max(n, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape, dtype=np.int64))).reshape(shape)
+
+    def free(self) -> None:
+        if self.ptr:
+            self.array = None
+            check(lib.ib200_pinned_free(self.ctx.handle, self.ptr))
+            self.ptr = None
+
+
+class Context:
+    """One GPU context (``ib200_ctx_create``).  Creation fails loudly when no B200 is visible."""
+
+    def __init__(self, device: int = 0):
+        h = C.c_void_p()
+        check(lib.ib200_ctx_create(int(device), C.byref(h)))
+        self.handle = h
+        self.device = int(device)
+
+    # -- housekeeping ---------------------------------------------------------------------------
+    def close(self) -> None:
+        if self.handle:
+            check(lib.ib200_ctx_destroy(self.handle))
+            self.handle = None
+
+    def synchronize(self) -> None:
+        check(lib.ib200_ctx_synchronize(self.handle))
+
+    def set_stream(self, cuda_stream: int | None) -> None:
+        check(lib.ib200_ctx_set_stream(self.handle, C.c_void_p(cuda_stream or 0)))
+
+    def set_force_generic(self, on: bool) -> None:
+        check(lib.ib200_ctx_set_force_generic(self.handle, int(bool(on))))
+
+    def set_chunk_elements(self, n: int) -> None:
+        check(lib.ib200_ctx_set_chunk_elements(self.handle, int(n)))
+
+    def clear_cache(self) -> None:
+        check(lib.ib200_ctx_clear_cache(self.handle))
+
+    def info(self) -> dict:
+        name = C.create_string_buffer(256)
+        sm, cc, mem = C.c_int(), C.c_int(), C.c_size_t()
+        check(lib.ib200_ctx_info(self.handle, name, 256, C.byref(sm), C.byref(cc), C.byref(mem)))
+        return {"name": name.value.decode(), "sm_count": sm.value, "cc": cc.value, "mem_bytes": mem.value}
+
+    def stats(self) -> dict:
+        n, t = C.c_ulonglong(), C.c_uint()
+        check(lib.ib200_ctx_stats(self.handle, C.byref(n), C.byref(t)))
+        return {"kernel_launches": n.value, "cached_tables": t.value}
+
+    def alloc(self, nbytes: int) -> DeviceBuffer:
+        return DeviceBuffer(self, nbytes)
+
+    def pinned(self, shape, dtype=np.float64) -> PinnedArray:
+        return PinnedArray(self, shape, dtype)
+
+    def timer_start(self, slot: int = 0) -> None:
+        check(lib.ib200_timer_start(self.handle, slot))
+
+    def timer_stop(self, slot: int = 0) -> None:
+        check(lib.ib200_timer_stop(self.handle, slot))
+
+    def timer_ms(self, slot: int = 0) -> float:
+        ms = C.c_float()
+        check(lib.ib200_timer_elapsed_ms(self.handle, slot, C.byref(ms)))
+        return float(ms.value)
+
+    # -- K1 ----------------------------------------------------------------------------------------
+    def reconstruct(self, basis, rules, dofs, deriv_masks=(0,), out=None, where=HOST, n_elements=None):
+        """dofs[E][N] -> out[E][n_fields][Q]   (ib200_reconstruct_batch)"""
+        N, Q = _n_basis(basis), _n_points(rules)
+        masks = (C.c_uint * len(deriv_masks))(*[int(m) for m in deriv_masks])
+        if where == HOST:
+            dofs = _as_in(dofs, (-1, N))
+            E = dofs.shape[0]
+            if out is None:
+                out = np.empty((E, len(deriv_masks), Q))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_reconstruct_batch(self.handle, len(basis), basis_specs(basis), rule_specs(rules), E, _ptr(dofs),
+                                          len(deriv_masks), masks, _ptr(out), where))
+        return out
+
+    # -- K0 ----------------------------------------------------------------------------------------
+    def geometry(self, geom_basis, rules, geom_dofs, n_phys, want=("coords", "det", "jinv"), where=HOST, n_elements=None,
+                 coords=None, det=None, jinv=None):
+        """geom_dofs[E][n_phys][Ng] -> coords[E][n_phys][1+d][Q], det[E][Q], jinv[E][Q][d][n_phys]"""
+        Ng, Q, d = _n_basis(geom_basis), _n_points(rules), len(geom_basis)
+        if where == HOST:
+            geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
+            E = geom_dofs.shape[0]
+            coords = np.empty((E, n_phys, 1 + d, Q)) if "coords" in want else None
+            det = np.empty((E, Q)) if "det" in want else None
+            jinv = np.empty((E, Q, d, n_phys)) if "jinv" in want else None
+        else:
+            E = int(n_elements)
+        check(lib.ib200_geometry_batch(self.handle, d, n_phys, basis_specs(geom_basis), rule_specs(rules), E,
+                                       _ptr(geom_dofs), _ptr(coords), _ptr(det), _ptr(jinv), where))
+        return coords, det, jinv
+
+    # -- K2 ----------------------------------------------------------------------------------------
+    def mass_matrix(self, basis_in, basis_out, rules, n_elements, weight=None, deriv_dim_in=-1, out=None, where=HOST):
+        """-> out[E][N_out][N_in]   (ib200_mass_matrix_batch); weight[E][Q] or None"""
+        Nin, Nout, Q = _n_basis(basis_in), _n_basis(basis_out), _n_points(rules)
+        E = int(n_elements)
+        if where == HOST:
+            if weight is not None:
+                weight = _as_in(weight, (E, Q))
+            if out is None:
+                out = np.empty((E, Nout, Nin))
+        check(lib.ib200_mass_matrix_batch(self.handle, len(rules), basis_specs(basis_in), basis_specs(basis_out),
+                                          rule_specs(rules), E, _ptr(weight), int(deriv_dim_in), _ptr(out), where))
+        return out
+
+    def mass_matrix_mapped(self, basis_in, basis_out, rules, geom_basis, geom_dofs, n_phys, idx_in=-1, idx_out=0, out=None,
+                           where=HOST, n_elements=None):
+        """geometry fused: geom_dofs[E][n_phys][Ng] -> out[E][N_out][N_in]   (ib200_mass_matrix_mapped_batch)"""
+        Nin, Nout, Ng = _n_basis(basis_in), _n_basis(basis_out), _n_basis(geom_basis)
+        if where == HOST:
+            geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
+            E = geom_dofs.shape[0]
+            if out is None:
+                out = np.empty((E, Nout, Nin))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_mass_matrix_mapped_batch(self.handle, len(rules), basis_specs(basis_in), basis_specs(basis_out),
+                                                 rule_specs(rules), n_phys, basis_specs(geom_basis), E, _ptr(geom_dofs),
+                                                 int(idx_in), int(idx_out), _ptr(out), where))
+        return out
+
+    # -- K3 ----------------------------------------------------------------------------------------
+    def l2_dual(self, basis, rules, fvals, det=None, out=None, where=HOST, n_elements=None):
+        """fvals[E][Q] (, det[E][Q]) -> out[E][N]   (ib200_l2_dual_batch)"""
+        N, Q = _n_basis(basis), _n_points(rules)
+        if where == HOST:
+            fvals = _as_in(fvals, (-1, Q))
+            E = fvals.shape[0]
+            if det is not None:
+                det = _as_in(det, (E, Q))
+            if out is None:
+                out = np.empty((E, N))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_l2_dual_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), E, _ptr(fvals),
+                                      _ptr(det), _ptr(out), where))
+        return out
+
+    def l2_dual_mapped(self, basis, rules, geom_basis, geom_dofs, n_phys, fvals, out=None, where=HOST, n_elements=None):
+        """geometry fused   (ib200_l2_dual_mapped_batch)"""
+        N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if where == HOST:
+            fvals = _as_in(fvals, (-1, Q))
+            E = fvals.shape[0]
+            geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
+            if out is None:
+                out = np.empty((E, N))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_l2_dual_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
+                                             basis_specs(geom_basis), E, _ptr(geom_dofs), _ptr(fvals), _ptr(out), where))
+        return out
+
+    # -- N1 ----------------------------------------------------------------------------------------
+    def spd_solve(self, mass, rhs, where=HOST, n=None, n_elements=None):
+        """Solve mass[e] u = rhs[e] for every element (Cholesky on the GPU); returns u[E][N]."""
+        if where == HOST:
+            rhs = np.array(rhs, dtype=np.float64, order="C", copy=True)
+            E, n = rhs.shape
+            mass = np.array(mass, dtype=np.float64, order="C", copy=True).reshape(E, n, n)
+        else:
+            E = int(n_elements)
+        check(lib.ib200_spd_solve_batch(self.handle, int(n), E, _ptr(mass), _ptr(rhs), where))
+        return rhs
+
+
+# ---- default context (lazy; one per process) -----------------------------------------------------------
+_default_ctx: Context | None = None
+_default_lock = threading.Lock()
+
+
+def device_count() -> int:
+    n = C.c_int()
+    code = lib.ib200_device_count(C.byref(n))
+    return n.value if code == 0 else 0
+
+
+def default_context() -> Context:
+    """The process-wide context on device ``$LOCAL_RANK`` (or 0).  Raises when no GPU is usable --
+    the batched path has no CPU implementation."""
+    global _default_ctx
+    with _default_lock:
+        if _default_ctx is None:
+            import os
+
+            _default_ctx = Context(int(os.environ.get("INTERP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0"))))
+        return _default_ctx
+
+
+# ---- host tables (no GPU needed) -----------------------------------------------------------------------------
+def rule_1d(method, order):
+    x = np.empty(order + 1)
+    w = np.empty(order + 1)
+    acc = C.c_uint()
+    check(lib.ib200_rule_1d(rule_specs([(method, order)])[0], x.ctypes.data_as(_lib._dp), w.ctypes.data_as(_lib._dp), C.byref(acc)))
+    return x, w, acc.value
+
+
+def lagrange_roots(btype, order):
+    r = np.empty(order + 1)
+    check(lib.ib200_lagrange_roots(basis_specs([(btype, order)])[0], r.ctypes.data_as(_lib._dp)))
+    return r
+
+
+def basis_table_1d(basis, rule):
+    (bt, bo), (rm, ro) = basis, rule
+    B = np.empty((bo + 1, ro + 1))
+    D = np.empty((bo + 1, ro + 1))
+    check(lib.ib200_basis_table_1d(basis_specs([basis])[0], rule_specs([rule])[0], B.ctypes.data_as(_lib._dp),
+                                   D.ctypes.data_as(_lib._dp)))
+    return B, D
+
+
+def integration_space_weights(rules):
+    W = np.empty([o + 1 for _, o in rules])
+    check(lib.ib200_integration_space_weights(len(rules), rule_specs(rules), W.ctypes.data_as(_lib._dp)))
+    return W
+
+
+def integration_space_nodes(rules):
+    X = np.empty([len(rules)] + [o + 1 for _, o in rules])
+    check(lib.ib200_integration_space_nodes(len(rules), rule_specs(rules), X.ctypes.data_as(_lib._dp)))
+    return X
+
+
+def values_at_integration_nodes(basis, rules):
+    out = np.empty([o + 1 for _, o in rules] + [o + 1 for _, o in basis])
+    check(lib.ib200_values_at_integration_nodes(len(rules), basis_specs(basis), rule_specs(rules), out.ctypes.data_as(_lib._dp)))
+    return out
+
+
+def basis_at_points(basis, x, derivative=False):
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    out = np.empty(x.shape + (basis[1] + 1,))
+    args = (None, out.ctypes.data_as(_lib._dp)) if derivative else (out.ctypes.data_as(_lib._dp), None)
+    check(lib.ib200_basis_at_points(basis_specs([basis])[0], x.size, x.ctypes.data_as(_lib._dp), *args))
+    return out
+
+
+def function_space_evaluate(basis, xs):
+    xs = [np.ascontiguousarray(x, dtype=np.float64) for x in xs]
+    shape = xs[0].shape
+    out = np.empty(shape + tuple(o + 1 for _, o in basis))
+    ptrs = (_lib._dp * len(xs))(*[x.ctypes.data_as(_lib._dp) for x in xs])
+    check(lib.ib200_function_space_evaluate(len(basis), basis_specs(basis), xs[0].size, ptrs, out.ctypes.data_as(_lib._dp)))
+    return out

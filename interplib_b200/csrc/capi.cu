@@ -1,0 +1,972 @@
+// C ABI of libinterp_b200.so (include/interp_b200.h): argument checking, the context with its device table
+// cache, host<->device staging for host-pointer calls, and dispatch to the CUDA kernels.
+#include <algorithm>
+#include <string>
+
+#include "ctx.cuh"
+
+// ---- errors -----------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+int ib200_fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+extern "C" const char *ib200_last_error(void)
+{
+    return g_last_error.c_str();
+}
+
+extern "C" const char *ib200_version(void)
+{
+    return "interp_b200 0.1 (sm_100a, FP64)";
+}
+
+// names follow the reference's interp_error_str (src/common/error.c:9-24), messages are our own wording
+extern "C" const char *ib200_error_str(int code)
+{
+    switch (code)
+    {
+    case INTERP_SUCCESS: return "INTERP_SUCCESS";
+    case INTERP_ERROR_NOT_IN_DOMAIN: return "INTERP_ERROR_NOT_IN_DOMAIN";
+    case INTERP_ERROR_NOT_INCREASING: return "INTERP_ERROR_NOT_INCREASING";
+    case INTERP_ERROR_FAILED_ALLOCATION: return "INTERP_ERROR_FAILED_ALLOCATION";
+    case INTERP_ERROR_BAD_SYSTEM: return "INTERP_ERROR_BAD_SYSTEM";
+    case INTERP_ERROR_INVALID_ENUM: return "INTERP_ERROR_INVALID_ENUM";
+    case INTERP_ERROR_NOT_IN_REGISTRY: return "INTERP_ERROR_NOT_IN_REGISTRY";
+    case INTERP_ERROR_GEOID_OUT_OF_RANGE: return "INTERP_ERROR_GEOID_OUT_OF_RANGE";
+    case INTERP_ERROR_GEOID_NOT_VALID: return "INTERP_ERROR_GEOID_NOT_VALID";
+    case INTERP_ERROR_SURFACE_NOT_CLOSED: return "INTERP_ERROR_SURFACE_NOT_CLOSED";
+    case INTERP_ERROR_OBJECT_CONNECTED_TWICE: return "INTERP_ERROR_OBJECT_CONNECTED_TWICE";
+    case INTERP_ERROR_MATRIX_DIMS_MISMATCH: return "INTERP_ERROR_MATRIX_DIMS_MISMATCH";
+    case IB200_ERROR_CUDA: return "IB200_ERROR_CUDA";
+    case IB200_ERROR_NO_DEVICE: return "IB200_ERROR_NO_DEVICE";
+    case IB200_ERROR_BAD_ARGUMENT: return "IB200_ERROR_BAD_ARGUMENT";
+    case IB200_ERROR_UNSUPPORTED: return "IB200_ERROR_UNSUPPORTED";
+    default: return "Unknown";
+    }
+}
+
+extern "C" const char *ib200_error_msg(int code)
+{
+    switch (code)
+    {
+    case INTERP_SUCCESS: return "Success";
+    case INTERP_ERROR_NOT_IN_DOMAIN: return "Argument was outside of the domain";
+    case INTERP_ERROR_NOT_INCREASING: return "Input was not monotonically increasing";
+    case INTERP_ERROR_FAILED_ALLOCATION: return "Memory allocation failed";
+    case INTERP_ERROR_BAD_SYSTEM: return "System could not be solved";
+    case INTERP_ERROR_INVALID_ENUM: return "Enum value was not valid";
+    case INTERP_ERROR_NOT_IN_REGISTRY: return "Object was not in the registry";
+    case INTERP_ERROR_GEOID_OUT_OF_RANGE: return "Geometry id was out of range";
+    case INTERP_ERROR_GEOID_NOT_VALID: return "Geometry id was not valid";
+    case INTERP_ERROR_SURFACE_NOT_CLOSED: return "Surface was not closed";
+    case INTERP_ERROR_OBJECT_CONNECTED_TWICE: return "Object was connected twice";
+    case INTERP_ERROR_MATRIX_DIMS_MISMATCH: return "Matrix dimensions did not match";
+    case IB200_ERROR_CUDA: return "A CUDA call or kernel failed";
+    case IB200_ERROR_NO_DEVICE: return "No usable CUDA device (the batched path has no CPU fallback)";
+    case IB200_ERROR_BAD_ARGUMENT: return "Bad argument";
+    case IB200_ERROR_UNSUPPORTED: return "Request is outside the implemented envelope";
+    default: return "Unknown error";
+    }
+}
+
+// ---- host tables (thin checked wrappers around tables.c) ----------------------------------------------
+static int check_basis_type(basis_set_type_t t)
+{
+    if (t < BASIS_LEGENDRE || t > BASIS_BERNSTEIN)
+        return ib200_fail(INTERP_ERROR_INVALID_ENUM, "basis type %d is not valid", (int)t);
+    return INTERP_SUCCESS;
+}
+static int check_rule_type(integration_rule_type_t t)
+{
+    if (t != INTEGRATION_RULE_TYPE_GAUSS_LEGENDRE && t != INTEGRATION_RULE_TYPE_GAUSS_LOBATTO)
+        return ib200_fail(INTERP_ERROR_INVALID_ENUM, "integration rule type %d is not valid", (int)t);
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_rule_1d(integration_spec_t spec, double *nodes, double *weights, unsigned *accuracy)
+{
+    if (!nodes || !weights)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "nodes/weights must not be NULL");
+    IB_TRY(check_rule_type(spec.type));
+    return ib200_tables_rule(spec, nodes, weights, accuracy);
+}
+
+extern "C" int ib200_rule_order_for_accuracy(integration_rule_type_t type, unsigned accuracy, unsigned *order)
+{
+    if (!order)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "order must not be NULL");
+    IB_TRY(check_rule_type(type));
+    return ib200_tables_order_for_accuracy(type, accuracy, order);
+}
+
+extern "C" int ib200_lagrange_roots(basis_spec_t spec, double *roots)
+{
+    if (!roots)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "roots must not be NULL");
+    if (!ib200_tables_is_lagrange(spec.type))
+        return ib200_fail(INTERP_ERROR_INVALID_ENUM, "basis type %d has no nodes", (int)spec.type);
+    return ib200_tables_lagrange_roots(spec, roots);
+}
+
+extern "C" int ib200_basis_table_1d(basis_spec_t basis, integration_spec_t rule, double *values, double *derivatives)
+{
+    if (!values || !derivatives)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "values/derivatives must not be NULL");
+    IB_TRY(check_basis_type(basis.type));
+    IB_TRY(check_rule_type(rule.type));
+    return ib200_tables_basis(basis, rule, values, derivatives);
+}
+
+extern "C" int ib200_integration_space_weights(unsigned ndim, const integration_spec_t *rules, double *weights)
+{
+    if (!rules || !weights || ndim == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "rules/weights must not be NULL and ndim > 0");
+    for (unsigned k = 0; k < ndim; ++k)
+        IB_TRY(check_rule_type(rules[k].type));
+    return ib200_tables_space_weights(ndim, rules, weights);
+}
+
+extern "C" int ib200_integration_space_nodes(unsigned ndim, const integration_spec_t *rules, double *nodes)
+{
+    if (!rules || !nodes || ndim == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "rules/nodes must not be NULL and ndim > 0");
+    for (unsigned k = 0; k < ndim; ++k)
+        IB_TRY(check_rule_type(rules[k].type));
+    return ib200_tables_space_nodes(ndim, rules, nodes);
+}
+
+extern "C" int ib200_values_at_integration_nodes(unsigned ndim, const basis_spec_t *basis,
+                                                 const integration_spec_t *rules, double *out)
+{
+    if (!basis || !rules || !out || ndim == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/rules/out must not be NULL and ndim > 0");
+    for (unsigned k = 0; k < ndim; ++k)
+    {
+        IB_TRY(check_basis_type(basis[k].type));
+        IB_TRY(check_rule_type(rules[k].type));
+    }
+    return ib200_tables_values_at_nodes(ndim, basis, rules, out);
+}
+
+extern "C" int ib200_basis_at_points(basis_spec_t basis, size_t cnt, const double *x, double *values,
+                                     double *derivatives)
+{
+    if (!x && cnt)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "x must not be NULL");
+    IB_TRY(check_basis_type(basis.type));
+    return ib200_tables_basis_at_points(basis, cnt, x, values, derivatives);
+}
+
+extern "C" int ib200_function_space_evaluate(unsigned ndim, const basis_spec_t *basis, size_t cnt,
+                                             const double *const *x, double *out)
+{
+    if (!basis || !x || !out || ndim == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/x/out must not be NULL and ndim > 0");
+    for (unsigned k = 0; k < ndim; ++k)
+        IB_TRY(check_basis_type(basis[k].type));
+    return ib200_tables_function_space_evaluate(ndim, basis, cnt, x, out);
+}
+
+// ---- context ---------------------------------------------------------------------------------------
+extern "C" int ib200_device_count(int *count)
+{
+    if (!count)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "count must not be NULL");
+    int n = 0;
+    const cudaError_t err = cudaGetDeviceCount(&n);
+    if (err != cudaSuccess)
+    {
+        *count = 0;
+        return ib200_fail(IB200_ERROR_NO_DEVICE, "cudaGetDeviceCount: %s", cudaGetErrorString(err));
+    }
+    *count = n;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
+{
+    if (!out)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "out must not be NULL");
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+        return ib200_fail(IB200_ERROR_NO_DEVICE, "no CUDA device visible; the batched hot path has no CPU fallback");
+    if (device < 0 || device >= n)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "device %d out of range (0..%d)", device, n - 1);
+    ib200_ctx *ctx = new (std::nothrow) ib200_ctx;
+    if (!ctx)
+        return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "out of host memory");
+    ctx->device = device;
+    IB_CUDA(cudaSetDevice(device));
+    IB_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
+    if (ctx->prop.major < 10)
+    {
+        const int major = ctx->prop.major, minor = ctx->prop.minor;
+        delete ctx;
+        return ib200_fail(IB200_ERROR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device,
+                          major, minor);
+    }
+    IB_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+    for (int i = 0; i < 3; ++i)
+    {
+        IB_CUDA(cudaStreamCreateWithFlags(&ctx->io_stream[i], cudaStreamNonBlocking));
+        IB_CUDA(cudaEventCreateWithFlags(&ctx->io_event[i], cudaEventDisableTiming));
+    }
+    for (int i = 0; i < 8; ++i)
+        for (int j = 0; j < 2; ++j)
+            IB_CUDA(cudaEventCreate(&ctx->timer[i][j]));
+    *out = ctx;
+    return INTERP_SUCCESS;
+}
+
+static int ctx_check(ib200_ctx *ctx)
+{
+    if (!ctx)
+        return ib200_fail(IB200_ERROR_NO_DEVICE, "context is NULL (no CUDA device?); there is no CPU fallback");
+    const cudaError_t err = cudaSetDevice(ctx->device);
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "cudaSetDevice(%d): %s", ctx->device, cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_clear_cache(ib200_ctx_t *ctx)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    IB_CUDA(cudaDeviceSynchronize());
+    for (auto &kv : ctx->tables)
+        cudaFree(kv.second.d_values);
+    for (auto &kv : ctx->rules)
+        cudaFree(kv.second.d_nodes);
+    ctx->tables.clear();
+    ctx->rules.clear();
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_destroy(ib200_ctx_t *ctx)
+{
+    if (!ctx)
+        return INTERP_SUCCESS;
+    IB_TRY(ctx_check(ctx));
+    cudaDeviceSynchronize();
+    ib200_ctx_clear_cache(ctx);
+    for (int i = 0; i < 3; ++i)
+    {
+        cudaFree(ctx->stage_dev[i]);
+        cudaFreeHost(ctx->stage_pin[i]);
+        cudaStreamDestroy(ctx->io_stream[i]);
+        cudaEventDestroy(ctx->io_event[i]);
+    }
+    cudaFree(ctx->scratch);
+    for (int i = 0; i < 8; ++i)
+        for (int j = 0; j < 2; ++j)
+            cudaEventDestroy(ctx->timer[i][j]);
+    cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_synchronize(ib200_ctx_t *ctx)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_stream(ib200_ctx_t *ctx, void *cuda_stream)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_info(ib200_ctx_t *ctx, char *name, size_t len, int *sm_count, int *cc, size_t *mem_bytes)
+{
+    IB_TRY(ctx_check(ctx));
+    if (name && len)
+    {
+        std::strncpy(name, ctx->prop.name, len - 1);
+        name[len - 1] = 0;
+    }
+    if (sm_count)
+        *sm_count = ctx->prop.multiProcessorCount;
+    if (cc)
+        *cc = ctx->prop.major * 10 + ctx->prop.minor;
+    if (mem_bytes)
+        *mem_bytes = ctx->prop.totalGlobalMem;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_stats(ib200_ctx_t *ctx, unsigned long long *kernel_launches, unsigned *cached_tables)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (kernel_launches)
+        *kernel_launches = ctx->launches;
+    if (cached_tables)
+        *cached_tables = (unsigned)(ctx->tables.size() + ctx->rules.size());
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_force_generic(ib200_ctx_t *ctx, int on)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->force_generic = on != 0;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->chunk_elements = elements;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_device_alloc(ib200_ctx_t *ctx, size_t bytes, void **dptr)
+{
+    IB_TRY(ctx_check(ctx));
+    if (!dptr)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "dptr must not be NULL");
+    const cudaError_t err = cudaMalloc(dptr, bytes ? bytes : 1);
+    if (err != cudaSuccess)
+    {
+        cudaGetLastError();
+        return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(err));
+    }
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_device_free(ib200_ctx_t *ctx, void *dptr)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaFree(dptr));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_pinned_alloc(ib200_ctx_t *ctx, size_t bytes, void **hptr)
+{
+    IB_TRY(ctx_check(ctx));
+    if (!hptr)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "hptr must not be NULL");
+    const cudaError_t err = cudaMallocHost(hptr, bytes ? bytes : 1);
+    if (err != cudaSuccess)
+    {
+        cudaGetLastError();
+        return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "cudaMallocHost(%zu bytes): %s", bytes, cudaGetErrorString(err));
+    }
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_pinned_free(ib200_ctx_t *ctx, void *hptr)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaFreeHost(hptr));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_copy_h2d(ib200_ctx_t *ctx, void *dst_dev, const void *src_host, size_t bytes)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_copy_d2h(ib200_ctx_t *ctx, void *dst_host, const void *src_dev, size_t bytes)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_device_memset(ib200_ctx_t *ctx, void *dptr, int byte, size_t bytes)
+{
+    IB_TRY(ctx_check(ctx));
+    IB_CUDA(cudaMemsetAsync(dptr, byte, bytes, ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_timer_start(ib200_ctx_t *ctx, unsigned slot)
+{
+    IB_TRY(ctx_check(ctx));
+    if (slot >= 8)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "timer slot %u out of range", slot);
+    IB_CUDA(cudaEventRecord(ctx->timer[slot][0], ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_timer_stop(ib200_ctx_t *ctx, unsigned slot)
+{
+    IB_TRY(ctx_check(ctx));
+    if (slot >= 8)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "timer slot %u out of range", slot);
+    IB_CUDA(cudaEventRecord(ctx->timer[slot][1], ctx->stream));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_timer_elapsed_ms(ib200_ctx_t *ctx, unsigned slot, float *ms)
+{
+    IB_TRY(ctx_check(ctx));
+    if (slot >= 8 || !ms)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "bad timer slot or NULL output");
+    IB_CUDA(cudaEventSynchronize(ctx->timer[slot][1]));
+    IB_CUDA(cudaEventElapsedTime(ms, ctx->timer[slot][0], ctx->timer[slot][1]));
+    return INTERP_SUCCESS;
+}
+
+// ---- device table cache (the registries' device-side mirror) ----------------------------------------------
+int ctx_get_rule(ib200_ctx *ctx, integration_spec_t r, const DeviceRule **out)
+{
+    const auto key = std::make_tuple((int)r.type, r.order);
+    auto it = ctx->rules.find(key);
+    if (it == ctx->rules.end())
+    {
+        DeviceRule rule;
+        rule.m = (int)r.order + 1;
+        rule.h_nodes.resize(2 * (size_t)rule.m);
+        IB_TRY(ib200_tables_rule(r, rule.h_nodes.data(), rule.h_nodes.data() + rule.m, nullptr));
+        IB_CUDA(cudaMalloc(&rule.d_nodes, sizeof(double) * 2 * rule.m));
+        IB_CUDA(cudaMemcpy(rule.d_nodes, rule.h_nodes.data(), sizeof(double) * 2 * rule.m, cudaMemcpyHostToDevice));
+        it = ctx->rules.emplace(key, std::move(rule)).first;
+    }
+    *out = &it->second;
+    return INTERP_SUCCESS;
+}
+
+int ctx_get_table(ib200_ctx *ctx, basis_spec_t b, integration_spec_t r, const DeviceTable **out)
+{
+    const auto key = std::make_tuple((int)b.type, b.order, (int)r.type, r.order);
+    auto it = ctx->tables.find(key);
+    if (it == ctx->tables.end())
+    {
+        DeviceTable tab;
+        tab.n = (int)b.order + 1;
+        tab.m = (int)r.order + 1;
+        const size_t cnt = (size_t)tab.n * tab.m;
+        tab.h_values.resize(2 * cnt);
+        IB_TRY(ib200_tables_basis(b, r, tab.h_values.data(), tab.h_values.data() + cnt));
+        IB_CUDA(cudaMalloc(&tab.d_values, sizeof(double) * 2 * cnt));
+        IB_CUDA(cudaMemcpy(tab.d_values, tab.h_values.data(), sizeof(double) * 2 * cnt, cudaMemcpyHostToDevice));
+        it = ctx->tables.emplace(key, std::move(tab)).first;
+    }
+    *out = &it->second;
+    return INTERP_SUCCESS;
+}
+
+int ctx_make_op(ib200_ctx *ctx, unsigned ndim, const basis_spec_t *basis_in, const basis_spec_t *basis_out,
+                const integration_spec_t *rules, OpDesc *op, OpHost *host)
+{
+    if (ndim == 0 || ndim > IB200_MAX_DIM)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "reference dimension %u not supported by the batched kernels (1..%d)", ndim,
+                          (int)IB200_MAX_DIM);
+    if (!basis_in || !rules)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/rules must not be NULL");
+    std::memset(op, 0, sizeof *op);
+    std::memset(host, 0, sizeof *host);
+    op->ndim = (int)ndim;
+    long long n_in = 1, n_out = 1, q = 1;
+    for (unsigned k = 0; k < ndim; ++k)
+    {
+        IB_TRY(check_basis_type(basis_in[k].type));
+        IB_TRY(check_rule_type(rules[k].type));
+        const basis_spec_t bo = basis_out ? basis_out[k] : basis_in[k];
+        IB_TRY(check_basis_type(bo.type));
+        const DeviceTable *ti, *to;
+        const DeviceRule *r;
+        IB_TRY(ctx_get_table(ctx, basis_in[k], rules[k], &ti));
+        IB_TRY(ctx_get_table(ctx, bo, rules[k], &to));
+        IB_TRY(ctx_get_rule(ctx, rules[k], &r));
+        DimTab &d = op->dim[k];
+        d.n_in = ti->n;
+        d.n_out = to->n;
+        d.m = ti->m;
+        d.Bin = ti->d_values;
+        d.Din = ti->d_values + (size_t)ti->n * ti->m;
+        d.Bout = to->d_values;
+        d.w = r->d_nodes + r->m;
+        host->Bin[k] = ti->h_values.data();
+        host->Din[k] = ti->h_values.data() + (size_t)ti->n * ti->m;
+        host->Bout[k] = to->h_values.data();
+        host->Dout[k] = to->h_values.data() + (size_t)to->n * to->m;
+        host->w[k] = r->h_nodes.data() + r->m;
+        n_in *= d.n_in;
+        n_out *= d.n_out;
+        q *= d.m;
+    }
+    for (unsigned k = ndim; k < IB200_MAX_DIM; ++k)
+    {
+        op->dim[k].n_in = op->dim[k].n_out = op->dim[k].m = 1;
+    }
+    if (n_in > (1 << 24) || n_out > (1 << 24) || q > (1 << 24) || n_in * n_out > (1ll << 30))
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "element too large (N_in=%lld N_out=%lld Q=%lld)", n_in, n_out, q);
+    op->N_in = (int)n_in;
+    op->N_out = (int)n_out;
+    op->Q = (int)q;
+    return INTERP_SUCCESS;
+}
+
+int ctx_scratch(ib200_ctx *ctx, size_t bytes, void **out)
+{
+    if (ctx->scratch_bytes < bytes)
+    {
+        if (ctx->scratch)
+        {
+            IB_CUDA(cudaStreamSynchronize(ctx->stream));
+            IB_CUDA(cudaFree(ctx->scratch));
+            ctx->scratch = nullptr;
+            ctx->scratch_bytes = 0;
+        }
+        const cudaError_t err = cudaMalloc(&ctx->scratch, bytes);
+        if (err != cudaSuccess)
+        {
+            cudaGetLastError();
+            return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "cudaMalloc(%zu bytes of scratch): %s", bytes,
+                              cudaGetErrorString(err));
+        }
+        ctx->scratch_bytes = bytes;
+    }
+    *out = ctx->scratch;
+    return INTERP_SUCCESS;
+}
+
+// ---- batched execution: device pointers run in place, host pointers are streamed in chunks --------------------
+namespace
+{
+
+enum ArrayKind
+{
+    ARR_IN,
+    ARR_OUT,
+    ARR_INOUT,
+    ARR_SCRATCH
+};
+
+struct BatchArray
+{
+    ArrayKind kind;
+    void *ptr;        // user pointer (host or device); NULL allowed for optional arrays and for scratch
+    size_t elem_bytes; // bytes per element
+};
+
+bool host_pointer_is_pinned(const void *p)
+{
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
+
+int ensure_stage(ib200_ctx *ctx, int slot, size_t dev_bytes, size_t pin_bytes)
+{
+    if (ctx->stage_dev_bytes[slot] < dev_bytes)
+    {
+        if (ctx->stage_dev[slot])
+            IB_CUDA(cudaFree(ctx->stage_dev[slot]));
+        ctx->stage_dev[slot] = nullptr;
+        ctx->stage_dev_bytes[slot] = 0;
+        const cudaError_t err = cudaMalloc(&ctx->stage_dev[slot], dev_bytes);
+        if (err != cudaSuccess)
+        {
+            cudaGetLastError();
+            return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "cudaMalloc(%zu staging bytes): %s", dev_bytes,
+                              cudaGetErrorString(err));
+        }
+        ctx->stage_dev_bytes[slot] = dev_bytes;
+    }
+    if (ctx->stage_pin_bytes[slot] < pin_bytes)
+    {
+        if (ctx->stage_pin[slot])
+            IB_CUDA(cudaFreeHost(ctx->stage_pin[slot]));
+        ctx->stage_pin[slot] = nullptr;
+        ctx->stage_pin_bytes[slot] = 0;
+        const cudaError_t err = cudaMallocHost(&ctx->stage_pin[slot], pin_bytes);
+        if (err != cudaSuccess)
+        {
+            cudaGetLastError();
+            return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "cudaMallocHost(%zu staging bytes): %s", pin_bytes,
+                              cudaGetErrorString(err));
+        }
+        ctx->stage_pin_bytes[slot] = pin_bytes;
+    }
+    return INTERP_SUCCESS;
+}
+
+inline size_t align_up(size_t v, size_t a)
+{
+    return (v + a - 1) / a * a;
+}
+
+// launch(cfg, first_element, n_elements, device pointers in `arrays` order) -> int
+template <class Launch>
+int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int where, size_t max_device_chunk, Launch launch)
+{
+    const int n_arr = (int)arrays.size();
+    if (where == IB200_DEVICE)
+    {
+        LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+        // scratch arrays come from the context; bound them by running sub-chunks
+        size_t scratch_per_elem = 0;
+        for (auto &a : arrays)
+            if (a.kind == ARR_SCRATCH)
+                scratch_per_elem += align_up(a.elem_bytes, 8);
+        size_t chunk = E;
+        if (scratch_per_elem)
+        {
+            const size_t budget = (size_t)512 << 20;
+            chunk = std::max<size_t>(1024, budget / scratch_per_elem);
+            if (max_device_chunk)
+                chunk = std::min(chunk, max_device_chunk);
+            chunk = std::min(chunk, E);
+        }
+        char *scratch = nullptr;
+        if (scratch_per_elem && E)
+        {
+            void *p;
+            IB_TRY(ctx_scratch(ctx, chunk * scratch_per_elem + 256 * n_arr, &p));
+            scratch = (char *)p;
+        }
+        std::vector<void *> dev(n_arr);
+        for (size_t first = 0; first < E || (E == 0 && first == 0); first += std::max<size_t>(chunk, 1))
+        {
+            const size_t cnt = std::min(chunk, E - first);
+            size_t off = 0;
+            for (int i = 0; i < n_arr; ++i)
+            {
+                if (arrays[i].kind == ARR_SCRATCH)
+                {
+                    dev[i] = scratch + off;
+                    off = align_up(off + chunk * arrays[i].elem_bytes, 256);
+                }
+                else
+                {
+                    dev[i] = arrays[i].ptr ? (char *)arrays[i].ptr + first * arrays[i].elem_bytes : nullptr;
+                }
+            }
+            IB_TRY(launch(cfg, first, cnt, dev.data()));
+            if (E == 0)
+                break;
+        }
+        return INTERP_SUCCESS;
+    }
+    if (where != IB200_HOST)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
+    if (E == 0)
+        return INTERP_SUCCESS;
+
+    // ---- host pointers: three slots, each with its own stream, device slab and pinned slab -----------------
+    size_t per_elem = 0;
+    for (auto &a : arrays)
+        if (a.ptr || a.kind == ARR_SCRATCH)
+            per_elem += a.elem_bytes;
+    size_t chunk = ctx->chunk_elements;
+    if (chunk == 0)
+    {
+        const size_t target = (size_t)48 << 20; // bytes per chunk: large enough to saturate PCIe, small enough to pipeline
+        chunk = std::max<size_t>(256, target / std::max<size_t>(per_elem, 1));
+    }
+    chunk = std::min(chunk, E);
+    std::vector<bool> pinned(n_arr, false);
+    size_t dev_bytes = 0, pin_bytes = 0;
+    std::vector<size_t> dev_off(n_arr, 0), pin_off(n_arr, 0);
+    for (int i = 0; i < n_arr; ++i)
+    {
+        if (!arrays[i].ptr && arrays[i].kind != ARR_SCRATCH)
+            continue;
+        dev_off[i] = dev_bytes;
+        dev_bytes = align_up(dev_bytes + chunk * arrays[i].elem_bytes, 256);
+        if (arrays[i].kind == ARR_SCRATCH)
+            continue;
+        pinned[i] = host_pointer_is_pinned(arrays[i].ptr);
+        if (!pinned[i])
+        {
+            pin_off[i] = pin_bytes;
+            pin_bytes = align_up(pin_bytes + chunk * arrays[i].elem_bytes, 256);
+        }
+    }
+    const int n_slots = 3;
+    for (int s = 0; s < n_slots; ++s)
+        IB_TRY(ensure_stage(ctx, s, dev_bytes, std::max<size_t>(pin_bytes, 1)));
+
+    struct Pending
+    {
+        bool busy = false;
+        size_t first = 0, cnt = 0;
+    } pending[3];
+    auto drain = [&](int s) -> int {
+        if (!pending[s].busy)
+            return INTERP_SUCCESS;
+        IB_CUDA(cudaEventSynchronize(ctx->io_event[s]));
+        for (int i = 0; i < n_arr; ++i)
+        {
+            const BatchArray &a = arrays[i];
+            if (!a.ptr || pinned[i] || (a.kind != ARR_OUT && a.kind != ARR_INOUT))
+                continue;
+            std::memcpy((char *)a.ptr + pending[s].first * a.elem_bytes, (char *)ctx->stage_pin[s] + pin_off[i],
+                        pending[s].cnt * a.elem_bytes);
+        }
+        pending[s].busy = false;
+        return INTERP_SUCCESS;
+    };
+
+    std::vector<void *> dev(n_arr);
+    int slot = 0;
+    for (size_t first = 0; first < E; first += chunk, slot = (slot + 1) % n_slots)
+    {
+        const size_t cnt = std::min(chunk, E - first);
+        IB_TRY(drain(slot));
+        cudaStream_t st = ctx->io_stream[slot];
+        for (int i = 0; i < n_arr; ++i)
+        {
+            const BatchArray &a = arrays[i];
+            dev[i] = (a.ptr || a.kind == ARR_SCRATCH) ? (char *)ctx->stage_dev[slot] + dev_off[i] : nullptr;
+            if (!a.ptr || (a.kind != ARR_IN && a.kind != ARR_INOUT))
+                continue;
+            const char *src = (const char *)a.ptr + first * a.elem_bytes;
+            if (!pinned[i])
+            {
+                std::memcpy((char *)ctx->stage_pin[slot] + pin_off[i], src, cnt * a.elem_bytes);
+                src = (const char *)ctx->stage_pin[slot] + pin_off[i];
+            }
+            IB_CUDA(cudaMemcpyAsync(dev[i], src, cnt * a.elem_bytes, cudaMemcpyHostToDevice, st));
+        }
+        LaunchCfg cfg{st, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+        IB_TRY(launch(cfg, first, cnt, dev.data()));
+        for (int i = 0; i < n_arr; ++i)
+        {
+            const BatchArray &a = arrays[i];
+            if (!a.ptr || (a.kind != ARR_OUT && a.kind != ARR_INOUT))
+                continue;
+            char *dst = pinned[i] ? (char *)a.ptr + first * a.elem_bytes : (char *)ctx->stage_pin[slot] + pin_off[i];
+            IB_CUDA(cudaMemcpyAsync(dst, dev[i], cnt * a.elem_bytes, cudaMemcpyDeviceToHost, st));
+        }
+        IB_CUDA(cudaEventRecord(ctx->io_event[slot], st));
+        pending[slot].busy = true;
+        pending[slot].first = first;
+        pending[slot].cnt = cnt;
+    }
+    for (int s = 0; s < n_slots; ++s)
+        IB_TRY(drain(s));
+    return INTERP_SUCCESS;
+}
+
+bool spaces_match(unsigned ndim, const basis_spec_t *a, const basis_spec_t *b)
+{
+    // function_spaces_match, /root/reference/src/python/mass_matrices.c:142-159
+    for (unsigned k = 0; k < ndim; ++k)
+        if (a[k].order != b[k].order || a[k].type != b[k].type)
+            return false;
+    return true;
+}
+
+} // namespace
+
+// ---- K1 ----------------------------------------------------------------------------------------------------
+extern "C" int ib200_reconstruct_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                       const integration_spec_t *rules, size_t n_elements, const double *dofs,
+                                       unsigned n_fields, const unsigned *deriv_masks, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (!deriv_masks || n_fields == 0 || n_fields > 8)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..8 fields and their derivative masks");
+    if (n_elements && (!dofs || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "dofs/out must not be NULL");
+    for (unsigned f = 0; f < n_fields; ++f)
+        if (deriv_masks[f] >> ndim)
+            return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "derivative mask 0x%x names a dimension >= %u", deriv_masks[f], ndim);
+    OpDesc op;
+    OpHost host;
+    IB_TRY(ctx_make_op(ctx, ndim, basis, nullptr, rules, &op, &host));
+    unsigned masks[8];
+    std::copy(deriv_masks, deriv_masks + n_fields, masks);
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)dofs, sizeof(double) * op.N_in},
+                                      {ARR_OUT, out, sizeof(double) * n_fields * op.Q}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           if (!cfg.force_generic)
+                           {
+                               const int res = launch_eval2d_fast(cfg, op, host, cnt, (const double *)dev[0], n_fields,
+                                                                  masks, (double *)dev[1]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
+                           return launch_reconstruct_generic(cfg, op, cnt, (const double *)dev[0], n_fields, masks,
+                                                             (double *)dev[1]);
+                       });
+}
+
+// ---- K0 ----------------------------------------------------------------------------------------------------
+static int check_geometry_dims(unsigned ndim, unsigned n_phys)
+{
+    if (n_phys < ndim)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT,
+                          "can not map %u reference dimensions to %u physical dimensions (need n_phys >= ndim)", ndim, n_phys);
+    if (n_phys > IB200_MAX_PHYS)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "at most %d physical dimensions (got %u)", (int)IB200_MAX_PHYS, n_phys);
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_geometry_batch(ib200_ctx_t *ctx, unsigned ndim, unsigned n_phys, const basis_spec_t *geom_basis,
+                                    const integration_spec_t *rules, size_t n_elements, const double *geom_dofs,
+                                    double *coords, double *det, double *jinv, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    IB_TRY(check_geometry_dims(ndim, n_phys));
+    if (n_elements && !geom_dofs)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs must not be NULL");
+    OpDesc op;
+    OpHost host;
+    IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &op, &host));
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * op.N_in},
+                                      {ARR_OUT, coords, sizeof(double) * n_phys * (1 + ndim) * op.Q},
+                                      {ARR_OUT, det, sizeof(double) * op.Q},
+                                      {ARR_OUT, jinv, sizeof(double) * op.Q * ndim * n_phys}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           return launch_geometry_generic(cfg, op, n_phys, cnt, (const double *)dev[0], (double *)dev[1],
+                                                          (double *)dev[2], (double *)dev[3], nullptr, -1, 0);
+                       });
+}
+
+// ---- K2 ----------------------------------------------------------------------------------------------------
+extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
+                                       const basis_spec_t *basis_out, const integration_spec_t *rules,
+                                       size_t n_elements, const double *weight, int deriv_dim_in, double *out,
+                                       int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (!basis_in || !basis_out)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis_in/basis_out must not be NULL");
+    if (n_elements && !out)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "out must not be NULL");
+    if (deriv_dim_in >= (int)ndim)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Index %d out of bounds for input space with %u dimensions.", deriv_dim_in,
+                          ndim);
+    OpDesc op;
+    OpHost host;
+    IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &op, &host));
+    const bool symmetric = spaces_match(ndim, basis_in, basis_out);
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)weight, sizeof(double) * op.Q},
+                                      {ARR_OUT, out, sizeof(double) * op.N_out * op.N_in}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[0],
+                                                      deriv_dim_in < 0 ? -1 : deriv_dim_in, (double *)dev[1]);
+                       });
+}
+
+extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
+                                              const basis_spec_t *basis_out, const integration_spec_t *rules,
+                                              unsigned n_phys, const basis_spec_t *geom_basis, size_t n_elements,
+                                              const double *geom_dofs, int idx_in, int idx_out, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    IB_TRY(check_geometry_dims(ndim, n_phys));
+    if (!basis_in || !basis_out || !geom_basis)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis_in/basis_out/geom_basis must not be NULL");
+    if (n_elements && (!out || !geom_dofs))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/out must not be NULL");
+    if (idx_in >= (int)ndim)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Index %d out of bounds for input space with %u dimensions.", idx_in, ndim);
+    if (idx_in >= 0 && (idx_out < 0 || idx_out >= (int)n_phys))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Index %d out of bounds for output space with %u dimensions.", idx_out,
+                          n_phys);
+    OpDesc op, gop;
+    OpHost host, ghost;
+    IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &op, &host));
+    IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
+    const bool symmetric = spaces_match(ndim, basis_in, basis_out);
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
+                                      {ARR_OUT, out, sizeof(double) * op.N_out * op.N_in},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, (const double *)dev[0], nullptr, nullptr,
+                                                          nullptr, (double *)dev[2], idx_in < 0 ? -1 : idx_in, idx_out));
+                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[2],
+                                                      idx_in < 0 ? -1 : idx_in, (double *)dev[1]);
+                       });
+}
+
+// ---- K3 ----------------------------------------------------------------------------------------------------
+extern "C" int ib200_l2_dual_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                   const integration_spec_t *rules, size_t n_elements, const double *fvals,
+                                   const double *det, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (n_elements && (!fvals || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "fvals/out must not be NULL");
+    OpDesc op;
+    OpHost host;
+    IB_TRY(ctx_make_op(ctx, ndim, basis, nullptr, rules, &op, &host));
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)fvals, sizeof(double) * op.Q},
+                                      {ARR_IN, (void *)det, sizeof(double) * op.Q},
+                                      {ARR_OUT, out, sizeof(double) * op.N_in}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           return launch_l2_generic(cfg, op, cnt, (const double *)dev[0], (const double *)dev[1],
+                                                    (double *)dev[2]);
+                       });
+}
+
+extern "C" int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                          const integration_spec_t *rules, unsigned n_phys,
+                                          const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                          const double *fvals, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    IB_TRY(check_geometry_dims(ndim, n_phys));
+    if (n_elements && (!fvals || !out || !geom_dofs))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/fvals/out must not be NULL");
+    OpDesc op, gop;
+    OpHost host, ghost;
+    IB_TRY(ctx_make_op(ctx, ndim, basis, nullptr, rules, &op, &host));
+    IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
+                                      {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
+                                      {ARR_OUT, out, sizeof(double) * op.N_in},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, (const double *)dev[0], nullptr, nullptr,
+                                                          nullptr, (double *)dev[3], -1, 0));
+                           return launch_l2_generic(cfg, op, cnt, (const double *)dev[1], (const double *)dev[3],
+                                                    (double *)dev[2]);
+                       });
+}
+
+// ---- N1 ----------------------------------------------------------------------------------------------------
+extern "C" int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
+                                     int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (n_elements && (!mass || !rhs))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "mass/rhs must not be NULL");
+    if (n == 0 || n > 4096)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "system size %u outside 1..4096", n);
+    std::vector<BatchArray> arrays = {{ARR_INOUT, mass, sizeof(double) * n * n}, {ARR_INOUT, rhs, sizeof(double) * n}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           return launch_spd_solve(cfg, n, cnt, (double *)dev[0], (double *)dev[1]);
+                       });
+}

@@ -1,0 +1,136 @@
+// Context, error plumbing and device-side table descriptors shared by the .cu files.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
+#include <vector>
+
+#include "../../include/interp_b200.h"
+#include "tables.h"
+
+// ---- error plumbing -----------------------------------------------------------------------------
+int ib200_fail(int code, const char *fmt, ...);
+
+#define IB_CUDA(call)                                                                                     \
+    do                                                                                                    \
+    {                                                                                                     \
+        const cudaError_t ib_err__ = (call);                                                              \
+        if (ib_err__ != cudaSuccess)                                                                      \
+            return ib200_fail(IB200_ERROR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(ib_err__), \
+                              __FILE__, __LINE__);                                                        \
+    } while (0)
+
+#define IB_TRY(call)                      \
+    do                                    \
+    {                                     \
+        const int ib_res__ = (call);      \
+        if (ib_res__ != INTERP_SUCCESS)   \
+            return ib_res__;              \
+    } while (0)
+
+// ---- device-side descriptors ----------------------------------------------------------------------
+// One tensor-product dimension of an operation.  Tables are basis-major [n][m] like the reference's
+// basis_set_t payload (src/basis/basis_set.h:28-55).
+struct DimTab
+{
+    int n_in;          // input-space basis count along this dimension
+    int n_out;         // output-space basis count (== n_in for single-space operations)
+    int m;             // quadrature points along this dimension
+    const double *Bin; // [n_in][m]
+    const double *Din; // [n_in][m]
+    const double *Bout; // [n_out][m]
+    const double *w;   // [m] rule weights
+};
+
+struct OpDesc
+{
+    int ndim;
+    DimTab dim[IB200_MAX_DIM];
+    int N_in, N_out, Q;
+};
+
+// Host copies of the same tables (the specialised kernels pass small tables through the kernel-parameter
+// constant bank).
+struct OpHost
+{
+    const double *Bin[IB200_MAX_DIM];
+    const double *Din[IB200_MAX_DIM];
+    const double *Bout[IB200_MAX_DIM];
+    const double *Dout[IB200_MAX_DIM];
+    const double *w[IB200_MAX_DIM];
+};
+
+// ---- host-side context ----------------------------------------------------------------------------
+struct DeviceTable
+{
+    double *d_values = nullptr; // [n][m] then derivatives [n][m]
+    std::vector<double> h_values; // host copy (values then derivatives)
+    int n = 0, m = 0;
+};
+struct DeviceRule
+{
+    double *d_nodes = nullptr; // [m] nodes then [m] weights
+    std::vector<double> h_nodes;
+    int m = 0;
+};
+
+struct ib200_ctx
+{
+    int device = 0;
+    cudaDeviceProp prop{};
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr; // stream work is queued on (own_stream unless adopted)
+    cudaStream_t io_stream[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t io_event[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t timer[8][2] = {};
+    std::mutex mutex;
+    std::map<std::tuple<int, unsigned, int, unsigned>, DeviceTable> tables;
+    std::map<std::tuple<int, unsigned>, DeviceRule> rules;
+    unsigned long long launches = 0;
+    bool force_generic = false;
+    size_t chunk_elements = 0;
+    // staging (host-pointer calls) and scratch (fused generic path)
+    void *stage_dev[3] = {nullptr, nullptr, nullptr};
+    size_t stage_dev_bytes[3] = {0, 0, 0};
+    void *stage_pin[3] = {nullptr, nullptr, nullptr};
+    size_t stage_pin_bytes[3] = {0, 0, 0};
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
+};
+
+int ctx_get_table(ib200_ctx *ctx, basis_spec_t b, integration_spec_t r, const DeviceTable **out);
+int ctx_get_rule(ib200_ctx *ctx, integration_spec_t r, const DeviceRule **out);
+int ctx_scratch(ib200_ctx *ctx, size_t bytes, void **out);
+
+// Build the device descriptor of an operation (uploads/caches tables as needed).
+int ctx_make_op(ib200_ctx *ctx, unsigned ndim, const basis_spec_t *basis_in, const basis_spec_t *basis_out,
+                const integration_spec_t *rules, OpDesc *op, OpHost *host);
+
+// ---- kernel launchers (device pointers, queued on `stream`) -----------------------------------------
+struct LaunchCfg
+{
+    cudaStream_t stream;
+    int sm_count;
+    bool force_generic;
+    unsigned long long *launch_counter;
+};
+
+int launch_reconstruct_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *dofs, unsigned n_fields,
+                               const unsigned *masks, double *out);
+int launch_geometry_generic(const LaunchCfg &cfg, const OpDesc &op, unsigned n_phys, size_t E, const double *geom_dofs,
+                            double *coords, double *det, double *jinv, double *weight_out, int w_idx_in, int w_idx_out);
+int launch_mass_generic(const LaunchCfg &cfg, const OpDesc &op, bool symmetric, size_t E, const double *weight,
+                        int deriv_dim_in, double *out);
+int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *fvals, const double *det, double *out);
+int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs);
+
+// Specialised (sum-factorised, templated) 2-D paths: return IB200_ERROR_UNSUPPORTED (without setting the
+// error text) when the shape is outside their instantiation list; the caller then uses the generic kernels.
+int launch_eval2d_fast(const LaunchCfg &cfg, const OpDesc &op, const OpHost &host, size_t E, const double *dofs,
+                       unsigned n_fields, const unsigned *masks, double *out);

@@ -1,0 +1,445 @@
+// Generic CUDA kernels: any reference dimension 1..3, any basis type / order per dimension, any rule.
+//
+// These are the "always correct" device path behind the C ABI: one thread per output value, the
+// tensor-product structure is used only to nest the loops (so an output costs prod(n) or prod(m)
+// fused multiply-adds, not d times that).  The specialised sum-factorised kernels in
+// kernels_eval2d.cu / kernels_mass2d.cu take over for the shapes on BASELINE.json's configs; these
+// kernels remain the device implementation for everything else and the cross-check for the fast
+// paths (ib200_ctx_set_force_generic).  There is no host implementation of any of them.
+//
+// Reference loops restated here (per element; results agree to ~1e-15 relative, summation order
+// differs): src/python/degrees_of_freedom.c:232-303 (reconstruct), src/python/mappings.c:448-542 +
+// src/operations/matrices.c:15-141 (Jacobian, Givens QR, left inverse), src/python/mass_matrices.c:264-335
+// and :486-560 (mass / gradient mass), python/interplib/integration.py:143-166 (L2 dual).
+#include "ctx.cuh"
+
+namespace
+{
+
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ void unflatten(int flat, const OpDesc &op, bool use_m, bool use_out, int idx[3])
+{
+    idx[0] = idx[1] = idx[2] = 0;
+    for (int k = op.ndim - 1; k >= 0; --k)
+    {
+        const int ext = use_m ? op.dim[k].m : (use_out ? op.dim[k].n_out : op.dim[k].n_in);
+        idx[k] = flat % ext;
+        flat /= ext;
+    }
+}
+
+// sum_i prod_k T_k[i_k][q_k] * dof[i], nested so the work is N fused multiply-adds.
+__device__ double tensor_contract(const OpDesc &op, unsigned mask, const int q[3], const double *__restrict__ dof)
+{
+    const DimTab &d0 = op.dim[0];
+    const double *T0 = ((mask & 1u) ? d0.Din : d0.Bin) + q[0];
+    if (op.ndim == 1)
+    {
+        double acc = 0.0;
+        for (int i0 = 0; i0 < d0.n_in; ++i0)
+            acc = fma(T0[i0 * d0.m], dof[i0], acc);
+        return acc;
+    }
+    const DimTab &d1 = op.dim[1];
+    const double *T1 = ((mask & 2u) ? d1.Din : d1.Bin) + q[1];
+    if (op.ndim == 2)
+    {
+        double acc = 0.0;
+        for (int i0 = 0; i0 < d0.n_in; ++i0)
+        {
+            double a1 = 0.0;
+            for (int i1 = 0; i1 < d1.n_in; ++i1)
+                a1 = fma(T1[i1 * d1.m], dof[i0 * d1.n_in + i1], a1);
+            acc = fma(T0[i0 * d0.m], a1, acc);
+        }
+        return acc;
+    }
+    const DimTab &d2 = op.dim[2];
+    const double *T2 = ((mask & 4u) ? d2.Din : d2.Bin) + q[2];
+    double acc = 0.0;
+    for (int i0 = 0; i0 < d0.n_in; ++i0)
+    {
+        double a1 = 0.0;
+        for (int i1 = 0; i1 < d1.n_in; ++i1)
+        {
+            double a2 = 0.0;
+            const double *row = dof + (size_t)(i0 * d1.n_in + i1) * d2.n_in;
+            for (int i2 = 0; i2 < d2.n_in; ++i2)
+                a2 = fma(T2[i2 * d2.m], row[i2], a2);
+            a1 = fma(T1[i1 * d1.m], a2, a1);
+        }
+        acc = fma(T0[i0 * d0.m], a1, acc);
+    }
+    return acc;
+}
+
+// ---- K1 generic: out[e][f][q] -----------------------------------------------------------------------
+struct MaskList
+{
+    unsigned n;
+    unsigned mask[8];
+};
+
+__global__ void __launch_bounds__(kThreads) reconstruct_generic_kernel(const __grid_constant__ OpDesc op, size_t E,
+                                                                       const double *__restrict__ dofs,
+                                                                       const __grid_constant__ MaskList fields,
+                                                                       double *__restrict__ out)
+{
+    const size_t per_elem = (size_t)fields.n * op.Q;
+    const size_t total = E * per_elem;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = t / per_elem;
+        const int r = (int)(t % per_elem);
+        const int f = r / op.Q;
+        int q[3];
+        unflatten(r % op.Q, op, true, false, q);
+        out[t] = tensor_contract(op, fields.mask[f], q, dofs + e * op.N_in);
+    }
+}
+
+// ---- K0 generic: geometry per (element, point) --------------------------------------------------------
+// Givens QR exactly as src/operations/matrices.c:15-86 orders its rotations (rows outer, columns inner),
+// R in place, Q^T accumulated; then det = prod diag(R) and the left inverse by back-substitution
+// (src/python/mappings.c:483-527).
+__device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, double *inv /*[cols][rows] or null*/)
+{
+    double qt[9];
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < rows; ++j)
+            qt[i * rows + j] = (i == j) ? 1.0 : 0.0;
+    if (rows > 1)
+    {
+        for (int row = 0; row < rows; ++row)
+            for (int col = 0; col < cols && col < row; ++col)
+            {
+                double c = r[col * cols + col];
+                double s = -r[row * cols + col];
+                const double mag = hypot(c, s);
+                if (mag < 1e-12)
+                    continue;
+                c /= mag;
+                s /= mag;
+                for (int k = col; k < cols; ++k)
+                {
+                    const double a = r[col * cols + k];
+                    const double b = r[row * cols + k];
+                    r[col * cols + k] = c * a - s * b;
+                    r[row * cols + k] = s * a + c * b;
+                }
+                r[row * cols + col] = 0.0;
+                for (int k = 0; k < rows; ++k)
+                {
+                    const double a = qt[col * rows + k];
+                    const double b = qt[row * rows + k];
+                    qt[col * rows + k] = c * a - s * b;
+                    qt[row * rows + k] = s * a + c * b;
+                }
+            }
+    }
+    double det = 1.0;
+    for (int i = 0; i < cols; ++i)
+        det *= r[i * cols + i];
+    *det_out = det;
+    if (inv)
+    {
+        for (int bc = 0; bc < rows; ++bc)
+            for (int row = cols; row > 0; --row)
+            {
+                double v = qt[(row - 1) * rows + bc];
+                for (int col = row; col < cols; ++col)
+                    v -= r[(row - 1) * cols + col] * inv[col * rows + bc];
+                inv[(row - 1) * rows + bc] = v / r[(row - 1) * cols + (row - 1)];
+            }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+    geometry_generic_kernel(const __grid_constant__ OpDesc op, int n_phys, size_t E, const double *__restrict__ gdofs,
+                            double *__restrict__ coords, double *__restrict__ det, double *__restrict__ jinv,
+                            double *__restrict__ weight_out, int w_idx_in, int w_idx_out)
+{
+    const int ndim = op.ndim;
+    const size_t total = E * (size_t)op.Q;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = t / op.Q;
+        const int qf = (int)(t % op.Q);
+        int q[3];
+        unflatten(qf, op, true, false, q);
+        double jac[9];
+        for (int a = 0; a < n_phys; ++a)
+        {
+            const double *dof = gdofs + (e * n_phys + a) * op.N_in;
+            if (coords)
+                coords[((e * n_phys + a) * (1 + ndim)) * op.Q + qf] = tensor_contract(op, 0u, q, dof);
+            for (int k = 0; k < ndim; ++k)
+            {
+                const double g = tensor_contract(op, 1u << k, q, dof);
+                jac[a * ndim + k] = g;
+                if (coords)
+                    coords[((e * n_phys + a) * (1 + ndim) + 1 + k) * op.Q + qf] = g;
+            }
+        }
+        if (det || jinv || weight_out)
+        {
+            double dv, inv[9];
+            qr_det_inverse(n_phys, ndim, jac, &dv, inv);
+            if (det)
+                det[t] = dv;
+            if (jinv)
+                for (int i = 0; i < ndim * n_phys; ++i)
+                    jinv[t * (size_t)(ndim * n_phys) + i] = inv[i];
+            if (weight_out)
+                weight_out[t] = (w_idx_in < 0) ? dv : dv * inv[w_idx_in * n_phys + w_idx_out];
+        }
+    }
+}
+
+// ---- K2 generic: out[e][j][i] --------------------------------------------------------------------------
+// One thread per entry of the lower triangle (symmetric) or of the full matrix; the quadrature sum is
+// nested dimension by dimension: sum_q0 P0 sum_q1 P1 sum_q2 P2 * wt[q], Pk = Bout_k[j_k][q_k]*Tin_k[i_k][q_k].
+__global__ void __launch_bounds__(kThreads)
+    mass_generic_kernel(const __grid_constant__ OpDesc op, int symmetric, size_t E, const double *__restrict__ weight,
+                        int deriv_in, double *__restrict__ out)
+{
+    const size_t per_elem = (size_t)op.N_out * op.N_in;
+    const size_t total = E * per_elem;
+    const DimTab &d0 = op.dim[0];
+    const DimTab &d1 = op.dim[1];
+    const DimTab &d2 = op.dim[2];
+    const int m1 = op.ndim > 1 ? d1.m : 1;
+    const int m2 = op.ndim > 2 ? d2.m : 1;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = t / per_elem;
+        const int r = (int)(t % per_elem);
+        const int jo = r / op.N_in, ii = r % op.N_in;
+        if (symmetric && ii > jo)
+            continue;
+        int bo[3], bi[3];
+        unflatten(jo, op, false, true, bo);
+        unflatten(ii, op, false, false, bi);
+        const double *wt = weight ? weight + e * op.Q : nullptr;
+        const double *Ti0 = (deriv_in == 0 ? d0.Din : d0.Bin) + bi[0] * d0.m;
+        const double *To0 = d0.Bout + bo[0] * d0.m;
+        double acc = 0.0;
+        for (int q0 = 0; q0 < d0.m; ++q0)
+        {
+            double a1 = 0.0;
+            if (op.ndim == 1)
+            {
+                a1 = wt ? wt[q0] : 1.0;
+            }
+            else
+            {
+                const double *Ti1 = (deriv_in == 1 ? d1.Din : d1.Bin) + bi[1] * d1.m;
+                const double *To1 = d1.Bout + bo[1] * d1.m;
+                for (int q1 = 0; q1 < m1; ++q1)
+                {
+                    double a2 = 0.0;
+                    if (op.ndim == 2)
+                    {
+                        a2 = wt ? wt[q0 * m1 + q1] : 1.0;
+                    }
+                    else
+                    {
+                        const double *Ti2 = (deriv_in == 2 ? d2.Din : d2.Bin) + bi[2] * d2.m;
+                        const double *To2 = d2.Bout + bo[2] * d2.m;
+                        for (int q2 = 0; q2 < m2; ++q2)
+                        {
+                            const double w = wt ? wt[(q0 * m1 + q1) * m2 + q2] : 1.0;
+                            a2 = fma(Ti2[q2] * To2[q2] * d2.w[q2], w, a2);
+                        }
+                    }
+                    a1 = fma(Ti1[q1] * To1[q1] * d1.w[q1], a2, a1);
+                }
+            }
+            acc = fma(Ti0[q0] * To0[q0] * d0.w[q0], a1, acc);
+        }
+        out[t] = acc;
+        if (symmetric && ii != jo)
+            out[e * per_elem + (size_t)ii * op.N_in + jo] = acc;
+    }
+}
+
+// ---- K3 generic: out[e][i] = sum_q f[q] W[q] det[q] Phi_i(q) ------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+    l2_generic_kernel(const __grid_constant__ OpDesc op, size_t E, const double *__restrict__ fvals,
+                      const double *__restrict__ det, double *__restrict__ out)
+{
+    const size_t total = E * (size_t)op.N_in;
+    const DimTab &d0 = op.dim[0];
+    const DimTab &d1 = op.dim[1];
+    const DimTab &d2 = op.dim[2];
+    const int m1 = op.ndim > 1 ? d1.m : 1;
+    const int m2 = op.ndim > 2 ? d2.m : 1;
+    for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = t / op.N_in;
+        int bi[3];
+        unflatten((int)(t % op.N_in), op, false, false, bi);
+        const double *f = fvals + e * op.Q;
+        const double *dt = det ? det + e * op.Q : nullptr;
+        double acc = 0.0;
+        for (int q0 = 0; q0 < d0.m; ++q0)
+        {
+            double a1 = 0.0;
+            for (int q1 = 0; q1 < m1; ++q1)
+            {
+                double a2 = 0.0;
+                for (int q2 = 0; q2 < m2; ++q2)
+                {
+                    const int qf = (q0 * m1 + q1) * m2 + q2;
+                    double v = f[qf];
+                    if (dt)
+                        v *= dt[qf];
+                    if (op.ndim > 2)
+                        v *= d2.w[q2] * d2.Bin[bi[2] * d2.m + q2];
+                    a2 += v;
+                }
+                if (op.ndim > 1)
+                    a2 *= d1.w[q1] * d1.Bin[bi[1] * d1.m + q1];
+                a1 += a2;
+            }
+            acc = fma(d0.w[q0] * d0.Bin[bi[0] * d0.m + q0], a1, acc);
+        }
+        out[t] = acc;
+    }
+}
+
+// ---- N1: batched SPD solve, one warp per element, Cholesky in place in global/L2 ---------------------------
+// projection_l2_primal (python/interplib/integration.py:212-221) solves M u = b per element with LAPACK LU;
+// M is SPD (cond <= ~1e3 on these spaces) so Cholesky agrees to ~1e-14.
+__global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double *__restrict__ mass, double *__restrict__ rhs)
+{
+    const int lane = threadIdx.x & 31;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t e = warp; e < E; e += n_warps)
+    {
+        double *A = mass + e * (size_t)n * n;
+        double *b = rhs + e * (size_t)n;
+        // right-looking Cholesky, lower triangle
+        for (int k = 0; k < n; ++k)
+        {
+            __syncwarp();
+            const double akk = sqrt(A[k * n + k]);
+            __syncwarp();
+            if (lane == 0)
+                A[k * n + k] = akk;
+            for (int i = k + 1 + lane; i < n; i += 32)
+                A[i * n + k] /= akk;
+            __syncwarp();
+            for (int idx = lane; idx < (n - k - 1) * (n - k - 1); idx += 32)
+            {
+                const int i = k + 1 + idx / (n - k - 1);
+                const int j = k + 1 + idx % (n - k - 1);
+                if (j <= i)
+                    A[i * n + j] -= A[i * n + k] * A[j * n + k];
+            }
+        }
+        __syncwarp();
+        // forward then backward substitution (serial in k, parallel in rows)
+        for (int k = 0; k < n; ++k)
+        {
+            __syncwarp();
+            const double yk = b[k] / A[k * n + k];
+            __syncwarp();
+            if (lane == 0)
+                b[k] = yk;
+            for (int i = k + 1 + lane; i < n; i += 32)
+                b[i] -= A[i * n + k] * yk;
+        }
+        for (int k = n - 1; k >= 0; --k)
+        {
+            __syncwarp();
+            const double xk = b[k] / A[k * n + k];
+            __syncwarp();
+            if (lane == 0)
+                b[k] = xk;
+            for (int i = lane; i < k; i += 32)
+                b[i] -= A[k * n + i] * xk;
+        }
+        __syncwarp();
+    }
+}
+
+int grid_for(size_t total_threads, int sm_count)
+{
+    const size_t blocks = (total_threads + kThreads - 1) / kThreads;
+    const size_t cap = (size_t)sm_count * 16; // grid-stride beyond 16 resident CTAs per SM
+    return (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+int check_launch(const char *what)
+{
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}
+
+} // namespace
+
+int launch_reconstruct_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *dofs, unsigned n_fields,
+                               const unsigned *masks, double *out)
+{
+    if (n_fields > 8)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "at most 8 fields per reconstruct call (got %u)", n_fields);
+    MaskList ml{};
+    ml.n = n_fields;
+    for (unsigned f = 0; f < n_fields; ++f)
+        ml.mask[f] = masks[f];
+    if (E == 0 || n_fields == 0)
+        return INTERP_SUCCESS;
+    reconstruct_generic_kernel<<<grid_for(E * n_fields * op.Q, cfg.sm_count), kThreads, 0, cfg.stream>>>(op, E, dofs, ml, out);
+    ++*cfg.launch_counter;
+    return check_launch("reconstruct_generic_kernel");
+}
+
+int launch_geometry_generic(const LaunchCfg &cfg, const OpDesc &op, unsigned n_phys, size_t E, const double *geom_dofs,
+                            double *coords, double *det, double *jinv, double *weight_out, int w_idx_in, int w_idx_out)
+{
+    if (E == 0)
+        return INTERP_SUCCESS;
+    geometry_generic_kernel<<<grid_for(E * op.Q, cfg.sm_count), kThreads, 0, cfg.stream>>>(
+        op, (int)n_phys, E, geom_dofs, coords, det, jinv, weight_out, w_idx_in, w_idx_out);
+    ++*cfg.launch_counter;
+    return check_launch("geometry_generic_kernel");
+}
+
+int launch_mass_generic(const LaunchCfg &cfg, const OpDesc &op, bool symmetric, size_t E, const double *weight,
+                        int deriv_dim_in, double *out)
+{
+    if (E == 0)
+        return INTERP_SUCCESS;
+    mass_generic_kernel<<<grid_for(E * op.N_out * op.N_in, cfg.sm_count), kThreads, 0, cfg.stream>>>(
+        op, symmetric ? 1 : 0, E, weight, deriv_dim_in, out);
+    ++*cfg.launch_counter;
+    return check_launch("mass_generic_kernel");
+}
+
+int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *fvals, const double *det, double *out)
+{
+    if (E == 0)
+        return INTERP_SUCCESS;
+    l2_generic_kernel<<<grid_for(E * op.N_in, cfg.sm_count), kThreads, 0, cfg.stream>>>(op, E, fvals, det, out);
+    ++*cfg.launch_counter;
+    return check_launch("l2_generic_kernel");
+}
+
+int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs)
+{
+    if (E == 0 || n == 0)
+        return INTERP_SUCCESS;
+    const size_t warps = E;
+    size_t blocks = (warps * 32 + 127) / 128;
+    const size_t cap = (size_t)cfg.sm_count * 16;
+    if (blocks > cap)
+        blocks = cap;
+    spd_solve_kernel<<<(int)blocks, 128, 0, cfg.stream>>>((int)n, E, mass, rhs);
+    ++*cfg.launch_counter;
+    return check_launch("spd_solve_kernel");
+}

@@ -1,0 +1,121 @@
+"""CPU: pin the oracle (oracle/interp_oracle.c) -- bit-exact against the golden vectors the compiled reference
+generated (tests/golden/make_golden.py) and, where oracle/_ref is available, against the reference itself on
+fresh random inputs."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from interplib_b200 import synthetic as syn
+
+GOLD = Path(__file__).resolve().parent / "golden"
+
+
+def load(name):
+    return dict(np.load(GOLD / f"{name}.npz"))
+
+
+@pytest.mark.parametrize("name", ["c1", "c2", "c3", "c4", "c5"])
+def test_oracle_matches_golden(orc, name):
+    g = load(name)
+    cfg = syn.CONFIGS[name]
+    basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
+    E = g["geom"].shape[0]
+    coords, det, jinv = orc.geometry(gb, rules, g["geom"], cfg.n_phys)
+    assert np.array_equal(coords, g["coords"])
+    assert np.array_equal(det, g["det"])
+    assert np.array_equal(jinv, g["jinv"])
+    assert np.array_equal(orc.reconstruct(basis, rules, g["dofs"], list(g["recon_masks"])), g["recon"])
+    assert np.array_equal(orc.l2_dual(basis, rules, g["fvals"], det=det), g["l2_dual"])
+    if "mass" in g:
+        s = int(g["mass_stride"])
+        m = orc.mass(basis, basis, rules, E, det=det)
+        assert np.array_equal(m.reshape(E, -1)[:, ::s], g["mass"])
+        assert np.array_equal(m, np.swapaxes(m, 1, 2))  # exact mirror (mass_matrices.c:326-335)
+        assert np.array_equal(orc.mass(basis, basis, rules, 1).reshape(1, -1)[:, ::s], g["mass_ref_domain"])
+    if name == "c3":
+        for a, sa in enumerate(syn.C3_SPACES):
+            for b, sb in enumerate(syn.C3_SPACES):
+                assert np.array_equal(orc.mass(list(sb), list(sa), rules, E, det=det), g[f"block_{a}{b}"])
+    if name == "c5":
+        lower = [(t, o - 1) for t, o in basis]
+        for i in range(2):
+            for j in range(2):
+                kw = dict(det=det, jinv=jinv, n_phys=2, deriv_in=i, idx_out=j)
+                assert np.array_equal(orc.mass(basis, basis, rules, E, **kw), g[f"gradmass_{i}{j}"])
+                assert np.array_equal(orc.mass(basis, lower, rules, E, **kw), g[f"gradmass_mixed_{i}{j}"])
+
+
+def test_golden_inputs_are_the_synthetic_mesh():
+    for name in ("c1", "c2", "c5"):
+        g = load(name)
+        cfg = syn.CONFIGS[name]
+        for row, e in enumerate(g["elements"]):
+            assert np.array_equal(syn.geometry(cfg, int(e), 1)[0], g["geom"][row])
+
+
+RANDOM_SPACES = [
+    ([("lagrange-gauss-lobatto", 4)], [("gauss", 7)]),
+    ([("lagrange-gauss-lobatto", 6)] * 2, [("gauss", 7)] * 2),
+    ([("bernstein", 2), ("legendre", 3)], [("gauss", 4), ("gauss-lobatto", 3)]),
+    ([("lagrange-uniform", 2), ("lagrange-gauss", 1), ("lagrange-chebyshev-gauss", 2)], [("gauss", 2), ("gauss", 3), ("gauss-lobatto", 2)]),
+]
+
+
+@pytest.mark.parametrize("basis,rules", RANDOM_SPACES)
+def test_oracle_reconstruct_vs_reference(orc, refdrive, basis, rules):
+    rng = np.random.default_rng(7)
+    d = len(basis)
+    N = int(np.prod([o + 1 for _, o in basis]))
+    dofs = rng.random((5, N))
+    masks = [0] + [1 << k for k in range(d)] + ([3] if d > 1 else [])
+    assert np.array_equal(orc.reconstruct(basis, rules, dofs, masks), refdrive.reconstruct(basis, rules, dofs, masks))
+
+
+@pytest.mark.parametrize(
+    "gb,rules,n_phys",
+    [
+        ([("lagrange-uniform", 1)] * 2, [("gauss", 5)] * 2, 2),
+        ([("bernstein", 1)], [("gauss", 7)], 1),
+        ([("bernstein", 2)], [("gauss", 3)], 3),
+        ([("lagrange-uniform", 1)] * 2, [("gauss", 3)] * 2, 3),
+        ([("legendre", 1), ("bernstein", 3)], [("gauss", 2), ("gauss", 0)], 2),
+        ([("lagrange-uniform", 1)] * 3, [("gauss", 2)] * 3, 3),
+    ],
+)
+def test_oracle_geometry_vs_reference(orc, refdrive, gb, rules, n_phys):
+    rng = np.random.default_rng(11)
+    Ng = int(np.prod([o + 1 for _, o in gb]))
+    g = rng.random((4, n_phys, Ng))
+    c, dt, ji = orc.geometry(gb, rules, g, n_phys)
+    cr, dtr, jir = refdrive.geometry(gb, rules, g, n_phys)
+    assert np.array_equal(c, cr) and np.array_equal(dt, dtr) and np.array_equal(ji, jir)
+
+
+def test_oracle_mass_and_l2_vs_reference(orc, refdrive):
+    rng = np.random.default_rng(13)
+    gb = [("lagrange-uniform", 1)] * 2
+    rules = [("gauss", 5)] * 2
+    g = rng.random((3, 2, 4))
+    _, dt, ji = orc.geometry(gb, rules, g, 2)
+    b4 = [("lagrange-gauss-lobatto", 4)] * 2
+    bi = [("legendre", 2), ("bernstein", 3)]
+    bo = [("lagrange-uniform", 2), ("lagrange-gauss-lobatto", 4)]
+    assert np.array_equal(orc.mass(b4, b4, rules, 3, det=dt), refdrive.mass(b4, b4, rules, 3, gb, g, 2))
+    assert np.array_equal(orc.mass(b4, b4, rules, 2), refdrive.mass(b4, b4, rules, 2))
+    assert np.array_equal(orc.mass(bi, bo, rules, 3, det=dt), refdrive.mass(bi, bo, rules, 3, gb, g, 2))
+    for ii in range(2):
+        for io in range(2):
+            kw = dict(det=dt, jinv=ji, n_phys=2, deriv_in=ii, idx_out=io)
+            assert np.array_equal(orc.mass(bi, bo, rules, 3, **kw), refdrive.mass(bi, bo, rules, 3, gb, g, 2, idx_in=ii, idx_out=io))
+            assert np.array_equal(orc.mass(b4, b4, rules, 3, **kw), refdrive.mass(b4, b4, rules, 3, gb, g, 2, idx_in=ii, idx_out=io))
+            assert np.array_equal(orc.mass(bi, bo, rules, 2, deriv_in=ii, idx_out=io), refdrive.mass(bi, bo, rules, 2, idx_in=ii, idx_out=io))
+    f = rng.random((3, 36))
+    assert np.array_equal(orc.l2_dual(b4, rules, f, det=dt), refdrive.l2_dual(b4, rules, f, gb, g, 2))
+    assert np.array_equal(orc.l2_dual(b4, rules, f), refdrive.l2_dual(b4, rules, f))
+    # 3-D
+    b3 = [("legendre", 1), ("bernstein", 2), ("lagrange-gauss", 1)]
+    r3 = [("gauss", 2), ("gauss", 2), ("gauss-lobatto", 2)]
+    g3 = rng.random((2, 3, 8))
+    _, d3, j3 = orc.geometry([("lagrange-uniform", 1)] * 3, r3, g3, 3)
+    assert np.array_equal(orc.mass(b3, b3, r3, 2, det=d3), refdrive.mass(b3, b3, r3, 2, [("lagrange-uniform", 1)] * 3, g3, 3))
