@@ -250,6 +250,7 @@ extern "C" int ib200_ctx_clear_cache(ib200_ctx_t *ctx)
         cudaFree(kv.second.d_nodes);
     ctx->tables.clear();
     ctx->rules.clear();
+    ctx->plans.clear();
     return INTERP_SUCCESS;
 }
 
@@ -772,6 +773,23 @@ bool spaces_match(unsigned ndim, const basis_spec_t *a, const basis_spec_t *b)
     return true;
 }
 
+std::string plan_key(const char *tag, unsigned ndim, const basis_spec_t *bi, const basis_spec_t *bo, const integration_spec_t *r,
+                     const basis_spec_t *gb, int a, int b, int c, int d)
+{
+    std::string k(tag);
+    auto add = [&k](long v) { k += ':' + std::to_string(v); };
+    add(ndim);
+    for (unsigned i = 0; i < ndim; ++i)
+    {
+        add(bi[i].type), add(bi[i].order);
+        add(bo ? bo[i].type : -1), add(bo ? bo[i].order : 0);
+        add(r[i].type), add(r[i].order);
+        add(gb ? gb[i].type : -1), add(gb ? gb[i].order : 0);
+    }
+    add(a), add(b), add(c), add(d);
+    return k;
+}
+
 } // namespace
 
 // ---- K1 ----------------------------------------------------------------------------------------------------
@@ -862,12 +880,22 @@ extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
     OpHost host;
     IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &op, &host));
     const bool symmetric = spaces_match(ndim, basis_in, basis_out);
+    const int deriv = deriv_dim_in < 0 ? -1 : deriv_dim_in;
+    const bool match0 = spaces_match(1, basis_in, basis_out);
+    const bool match1 = ndim > 1 && spaces_match(1, basis_in + 1, basis_out + 1);
+    const std::string key = plan_key("mass", ndim, basis_in, basis_out, rules, nullptr, deriv, weight ? 1 : 0, -1, 0);
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)weight, sizeof(double) * op.Q},
                                       {ARR_OUT, out, sizeof(double) * op.N_out * op.N_in}};
     return run_batched(ctx, n_elements, arrays, where, 0,
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
-                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[0],
-                                                      deriv_dim_in < 0 ? -1 : deriv_dim_in, (double *)dev[1]);
+                           if (!cfg.force_generic && cnt)
+                           {
+                               const int res = launch_mass2d_fast(ctx, cfg, key, op, host, match0, match1, deriv, weight ? 1 : 0,
+                                                                  nullptr, -1, 0, cnt, (const double *)dev[0], (double *)dev[1]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
+                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[0], deriv, (double *)dev[1]);
                        });
 }
 
@@ -893,15 +921,35 @@ extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, c
     IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &op, &host));
     IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
     const bool symmetric = spaces_match(ndim, basis_in, basis_out);
+    const int deriv = idx_in < 0 ? -1 : idx_in;
+    const bool match0 = spaces_match(1, basis_in, basis_out);
+    const bool match1 = ndim > 1 && spaces_match(1, basis_in + 1, basis_out + 1);
+    // bilinear quads in the plane: the geometry prologue is fused into the mass kernel (no [E][Q] weight array)
+    const bool fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
+    const std::string key_fused = plan_key("massg", ndim, basis_in, basis_out, rules, geom_basis, deriv, 2, deriv, idx_out);
+    const std::string key_w = plan_key("mass", ndim, basis_in, basis_out, rules, nullptr, deriv, 1, -1, 0);
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
                                       {ARR_OUT, out, sizeof(double) * op.N_out * op.N_in},
                                       {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
     return run_batched(ctx, n_elements, arrays, where, 0,
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           if (!cfg.force_generic && cnt && fuse_geometry)
+                           {
+                               const int res = launch_mass2d_fast(ctx, cfg, key_fused, op, host, match0, match1, deriv, 2, &ghost,
+                                                                  deriv, idx_out, cnt, (const double *)dev[0], (double *)dev[1]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
                            IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, (const double *)dev[0], nullptr, nullptr,
-                                                          nullptr, (double *)dev[2], idx_in < 0 ? -1 : idx_in, idx_out));
-                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[2],
-                                                      idx_in < 0 ? -1 : idx_in, (double *)dev[1]);
+                                                          nullptr, (double *)dev[2], deriv, idx_out));
+                           if (!cfg.force_generic && cnt)
+                           {
+                               const int res = launch_mass2d_fast(ctx, cfg, key_w, op, host, match0, match1, deriv, 1, nullptr, -1,
+                                                                  0, cnt, (const double *)dev[2], (double *)dev[1]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
+                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[2], deriv, (double *)dev[1]);
                        });
 }
 

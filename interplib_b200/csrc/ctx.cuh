@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <string>
 #include <mutex>
 #include <tuple>
 #include <vector>
@@ -92,6 +94,7 @@ struct ib200_ctx
     std::mutex mutex;
     std::map<std::tuple<int, unsigned, int, unsigned>, DeviceTable> tables;
     std::map<std::tuple<int, unsigned>, DeviceRule> rules;
+    std::map<std::string, std::shared_ptr<void>> plans; // per-operation kernel plans (kernels_mass2d.cu)
     unsigned long long launches = 0;
     bool force_generic = false;
     size_t chunk_elements = 0;
@@ -134,3 +137,6 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
 // error text) when the shape is outside their instantiation list; the caller then uses the generic kernels.
 int launch_eval2d_fast(const LaunchCfg &cfg, const OpDesc &op, const OpHost &host, size_t E, const double *dofs,
                        unsigned n_fields, const unsigned *masks, double *out);
+int launch_mass2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
+                       bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in,
+                       int widx_out, size_t E, const double *wsrc, double *out);

@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(kThreads) reconstruct_generic_kernel(const __g
 // ---- K0 generic: geometry per (element, point) --------------------------------------------------------
 // Givens QR exactly as src/operations/matrices.c:15-86 orders its rotations (rows outer, columns inner),
 // R in place, Q^T accumulated; then det = prod diag(R) and the left inverse by back-substitution
-// (src/python/mappings.c:483-527).
+// (src/python/mappings.c:483-527).  Products and sums are rounded separately (no FMA contraction) like the
+// reference build, so apart from hypot() (<= 1 ulp in both libm and CUDA) the results are bit-identical.
 __device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, double *inv /*[cols][rows] or null*/)
 {
     double qt[9];
@@ -125,16 +126,16 @@ __device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, d
                 {
                     const double a = r[col * cols + k];
                     const double b = r[row * cols + k];
-                    r[col * cols + k] = c * a - s * b;
-                    r[row * cols + k] = s * a + c * b;
+                    r[col * cols + k] = __dsub_rn(__dmul_rn(c, a), __dmul_rn(s, b));
+                    r[row * cols + k] = __dadd_rn(__dmul_rn(s, a), __dmul_rn(c, b));
                 }
                 r[row * cols + col] = 0.0;
                 for (int k = 0; k < rows; ++k)
                 {
                     const double a = qt[col * rows + k];
                     const double b = qt[row * rows + k];
-                    qt[col * rows + k] = c * a - s * b;
-                    qt[row * rows + k] = s * a + c * b;
+                    qt[col * rows + k] = __dsub_rn(__dmul_rn(c, a), __dmul_rn(s, b));
+                    qt[row * rows + k] = __dadd_rn(__dmul_rn(s, a), __dmul_rn(c, b));
                 }
             }
     }
@@ -149,10 +150,42 @@ __device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, d
             {
                 double v = qt[(row - 1) * rows + bc];
                 for (int col = row; col < cols; ++col)
-                    v -= r[(row - 1) * cols + col] * inv[col * rows + bc];
+                    v = __dsub_rn(v, __dmul_rn(r[(row - 1) * cols + col], inv[col * rows + bc]));
                 inv[(row - 1) * rows + bc] = v / r[(row - 1) * cols + (row - 1)];
             }
     }
+}
+
+// Geometry is the ill-conditioned input of the path (coordinates are O(1), their differences O(h)), so the
+// coordinate maps are evaluated in the reference's own operation order -- i row-major, phi = T0*T1*T2,
+// val = val + phi*dof with separately rounded multiply and add (the reference is built without FMA
+// contraction) -- which makes the Jacobian entries bit-identical to compute_integration_point_values[_derivatives]
+// (src/python/degrees_of_freedom.c:232-303) instead of merely close.
+__device__ double tensor_contract_reference_order(const OpDesc &op, unsigned mask, const int q[3], const double *__restrict__ dof)
+{
+    const DimTab &d0 = op.dim[0];
+    const DimTab &d1 = op.dim[1];
+    const DimTab &d2 = op.dim[2];
+    const double *T0 = ((mask & 1u) ? d0.Din : d0.Bin) + q[0];
+    const double *T1 = op.ndim > 1 ? ((mask & 2u) ? d1.Din : d1.Bin) + q[1] : nullptr;
+    const double *T2 = op.ndim > 2 ? ((mask & 4u) ? d2.Din : d2.Bin) + q[2] : nullptr;
+    const int n1 = op.ndim > 1 ? d1.n_in : 1;
+    const int n2 = op.ndim > 2 ? d2.n_in : 1;
+    double val = 0.0;
+    for (int i0 = 0; i0 < d0.n_in; ++i0)
+    {
+        const double t0 = T0[i0 * d0.m];
+        for (int i1 = 0; i1 < n1; ++i1)
+        {
+            const double t01 = T1 ? __dmul_rn(t0, T1[i1 * d1.m]) : t0;
+            for (int i2 = 0; i2 < n2; ++i2)
+            {
+                const double phi = T2 ? __dmul_rn(t01, T2[i2 * d2.m]) : t01;
+                val = __dadd_rn(val, __dmul_rn(phi, dof[(i0 * n1 + i1) * n2 + i2]));
+            }
+        }
+    }
+    return val;
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -173,10 +206,10 @@ __global__ void __launch_bounds__(kThreads)
         {
             const double *dof = gdofs + (e * n_phys + a) * op.N_in;
             if (coords)
-                coords[((e * n_phys + a) * (1 + ndim)) * op.Q + qf] = tensor_contract(op, 0u, q, dof);
+                coords[((e * n_phys + a) * (1 + ndim)) * op.Q + qf] = tensor_contract_reference_order(op, 0u, q, dof);
             for (int k = 0; k < ndim; ++k)
             {
-                const double g = tensor_contract(op, 1u << k, q, dof);
+                const double g = tensor_contract_reference_order(op, 1u << k, q, dof);
                 jac[a * ndim + k] = g;
                 if (coords)
                     coords[((e * n_phys + a) * (1 + ndim) + 1 + k) * op.Q + qf] = g;
