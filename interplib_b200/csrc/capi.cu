@@ -965,11 +965,19 @@ extern "C" int ib200_l2_dual_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_
     OpDesc op;
     OpHost host;
     IB_TRY(ctx_make_op(ctx, ndim, basis, nullptr, rules, &op, &host));
+    const std::string key = plan_key("l2", ndim, basis, nullptr, rules, nullptr, det ? 1 : 0, 0, 0, 0);
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)fvals, sizeof(double) * op.Q},
                                       {ARR_IN, (void *)det, sizeof(double) * op.Q},
                                       {ARR_OUT, out, sizeof(double) * op.N_in}};
     return run_batched(ctx, n_elements, arrays, where, 0,
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           if (!cfg.force_generic && cnt)
+                           {
+                               const int res = launch_l2dual2d_fast(ctx, cfg, key, op, host, det ? 1 : 0, nullptr, cnt,
+                                                                    (const double *)dev[0], (const double *)dev[1], (double *)dev[2]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
                            return launch_l2_generic(cfg, op, cnt, (const double *)dev[0], (const double *)dev[1],
                                                     (double *)dev[2]);
                        });
@@ -989,14 +997,31 @@ extern "C" int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const
     OpHost host, ghost;
     IB_TRY(ctx_make_op(ctx, ndim, basis, nullptr, rules, &op, &host));
     IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
+    const bool fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
+    const std::string key = plan_key("l2g", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
+    const std::string key_w = plan_key("l2", ndim, basis, nullptr, rules, nullptr, 1, 0, 0, 0);
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
                                       {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
                                       {ARR_OUT, out, sizeof(double) * op.N_in},
                                       {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
     return run_batched(ctx, n_elements, arrays, where, 0,
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           if (!cfg.force_generic && cnt && fuse_geometry)
+                           {
+                               const int res = launch_l2dual2d_fast(ctx, cfg, key, op, host, 2, &ghost, cnt, (const double *)dev[1],
+                                                                    (const double *)dev[0], (double *)dev[2]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
                            IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, (const double *)dev[0], nullptr, nullptr,
                                                           nullptr, (double *)dev[3], -1, 0));
+                           if (!cfg.force_generic && cnt)
+                           {
+                               const int res = launch_l2dual2d_fast(ctx, cfg, key_w, op, host, 1, nullptr, cnt, (const double *)dev[1],
+                                                                    (const double *)dev[3], (double *)dev[2]);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
                            return launch_l2_generic(cfg, op, cnt, (const double *)dev[1], (const double *)dev[3],
                                                     (double *)dev[2]);
                        });

@@ -140,3 +140,5 @@ int launch_eval2d_fast(const LaunchCfg &cfg, const OpDesc &op, const OpHost &hos
 int launch_mass2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                        bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in,
                        int widx_out, size_t E, const double *wsrc, double *out);
+int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
+                         int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);

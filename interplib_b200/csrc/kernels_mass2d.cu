@@ -109,8 +109,13 @@ __device__ __forceinline__ double bilinear_ref_order(const double t0[2], const d
     return val;
 }
 
+constexpr int min_blocks_for(int M, int R)
+{
+    return (M <= 6 && R == 2) ? 3 : ((M <= 10 && R == 2) || M <= 6 ? 2 : 1);
+}
+
 template <int M, int R, bool SYMB, int CAP>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, min_blocks_for(M, R))
     mass2d_kernel(const __grid_constant__ MassParams<CAP> prm, const double *__restrict__ P1g, const int2 *__restrict__ bmap,
                   const double *__restrict__ gtab, size_t E, const double *__restrict__ wsrc, double *__restrict__ out)
 {
@@ -475,7 +480,10 @@ static int build_plan(const OpDesc &op, const OpHost &host, bool match0, bool ma
             continue;
         const int epe = G == 1 ? 32 / bgp : 1;
         const double util = (double)s.NB * epe / (double)(R * 32 * G);
-        if (util >= best_util - 1e-9)
+        // ties: the wider item set amortises the uniform coefficient loads better, but below ~9 points per
+        // dimension it costs a resident CTA (registers), so prefer R = 2 there
+        const bool better = util > best_util + 1e-9 || (util >= best_util - 1e-9 && M >= 9);
+        if (better)
         {
             best_util = util;
             best_R = R;
@@ -487,9 +495,9 @@ static int build_plan(const OpDesc &op, const OpHost &host, bool match0, bool ma
     s.BGp = (s.NB + R - 1) / R;
     s.G = s.BGp <= 32 ? 1 : (s.BGp + 31) / 32;
     s.EPE = s.G == 1 ? 32 / s.BGp : 1;
-    // panels: about 4 KB of output per element and panel, at least one j0
+    // panels: about 6 KB of staged output per engine and buffer (all EPE elements together), at least one j0
     const int row_block = n_out1 * s.N_in;
-    s.PJ = std::max(1, std::min(n_out0, (int)(4096 / (sizeof(double) * row_block))));
+    s.PJ = std::max(1, std::min(n_out0, (int)(6144 / (sizeof(double) * row_block * s.EPE))));
     s.n_panels = (n_out0 + s.PJ - 1) / s.PJ;
     s.panel_cap = ((s.PJ * row_block + 2) + 1) & ~1;
     const size_t panel_bytes = sizeof(double) * s.EPE * s.panel_cap;
