@@ -97,8 +97,8 @@ typedef struct
 
 enum
 {
-    IB200_MAX_DIM = 3,   /* reference dimensions supported by the batched kernels          */
-    IB200_MAX_PHYS = 3,  /* physical coordinates per point                                 */
+    IB200_MAX_DIM = 6,   /* reference dimensions supported by the batched kernels          */
+    IB200_MAX_PHYS = 6,  /* physical coordinates per point                                 */
     IB200_HOST = 0,
     IB200_DEVICE = 1,
 };

@@ -18,9 +18,12 @@ namespace
 
 constexpr int kThreads = 256;
 
-__device__ __forceinline__ void unflatten(int flat, const OpDesc &op, bool use_m, bool use_out, int idx[3])
+constexpr int MAXD = IB200_MAX_DIM;
+
+__device__ __forceinline__ void unflatten(int flat, const OpDesc &op, bool use_m, bool use_out, int idx[MAXD])
 {
-    idx[0] = idx[1] = idx[2] = 0;
+    for (int k = 0; k < MAXD; ++k)
+        idx[k] = 0;
     for (int k = op.ndim - 1; k >= 0; --k)
     {
         const int ext = use_m ? op.dim[k].m : (use_out ? op.dim[k].n_out : op.dim[k].n_in);
@@ -30,8 +33,35 @@ __device__ __forceinline__ void unflatten(int flat, const OpDesc &op, bool use_m
 }
 
 // sum_i prod_k T_k[i_k][q_k] * dof[i], nested so the work is N fused multiply-adds.
-__device__ double tensor_contract(const OpDesc &op, unsigned mask, const int q[3], const double *__restrict__ dof)
+// More than three reference dimensions (the reference accepts any count, e.g. tests/test_dofs.py:79 uses five):
+// plain loop over all basis functions with an incrementing multi-index, prod(n)*d multiplies per output.
+__device__ double tensor_contract_nd(const OpDesc &op, unsigned mask, const int q[MAXD], const double *__restrict__ dof)
 {
+    int idx[MAXD] = {0};
+    double acc = 0.0;
+    for (int i = 0; i < op.N_in; ++i)
+    {
+        double phi = 1.0;
+        for (int k = 0; k < op.ndim; ++k)
+        {
+            const DimTab &d = op.dim[k];
+            phi *= (((mask >> k) & 1u) ? d.Din : d.Bin)[idx[k] * d.m + q[k]];
+        }
+        acc = fma(phi, dof[i], acc);
+        for (int k = op.ndim - 1; k >= 0; --k)
+        {
+            if (++idx[k] < op.dim[k].n_in)
+                break;
+            idx[k] = 0;
+        }
+    }
+    return acc;
+}
+
+__device__ double tensor_contract(const OpDesc &op, unsigned mask, const int q[MAXD], const double *__restrict__ dof)
+{
+    if (op.ndim > 3)
+        return tensor_contract_nd(op, mask, q, dof);
     const DimTab &d0 = op.dim[0];
     const double *T0 = ((mask & 1u) ? d0.Din : d0.Bin) + q[0];
     if (op.ndim == 1)
@@ -93,7 +123,7 @@ __global__ void __launch_bounds__(kThreads) reconstruct_generic_kernel(const __g
         const size_t e = t / per_elem;
         const int r = (int)(t % per_elem);
         const int f = r / op.Q;
-        int q[3];
+        int q[MAXD];
         unflatten(r % op.Q, op, true, false, q);
         out[t] = tensor_contract(op, fields.mask[f], q, dofs + e * op.N_in);
     }
@@ -106,7 +136,7 @@ __global__ void __launch_bounds__(kThreads) reconstruct_generic_kernel(const __g
 // reference build, so apart from hypot() (<= 1 ulp in both libm and CUDA) the results are bit-identical.
 __device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, double *inv /*[cols][rows] or null*/)
 {
-    double qt[9];
+    double qt[IB200_MAX_PHYS * IB200_MAX_PHYS];
     for (int i = 0; i < rows; ++i)
         for (int j = 0; j < rows; ++j)
             qt[i * rows + j] = (i == j) ? 1.0 : 0.0;
@@ -161,28 +191,24 @@ __device__ void qr_det_inverse(int rows, int cols, double *r, double *det_out, d
 // val = val + phi*dof with separately rounded multiply and add (the reference is built without FMA
 // contraction) -- which makes the Jacobian entries bit-identical to compute_integration_point_values[_derivatives]
 // (src/python/degrees_of_freedom.c:232-303) instead of merely close.
-__device__ double tensor_contract_reference_order(const OpDesc &op, unsigned mask, const int q[3], const double *__restrict__ dof)
+__device__ double tensor_contract_reference_order(const OpDesc &op, unsigned mask, const int q[MAXD], const double *__restrict__ dof)
 {
-    const DimTab &d0 = op.dim[0];
-    const DimTab &d1 = op.dim[1];
-    const DimTab &d2 = op.dim[2];
-    const double *T0 = ((mask & 1u) ? d0.Din : d0.Bin) + q[0];
-    const double *T1 = op.ndim > 1 ? ((mask & 2u) ? d1.Din : d1.Bin) + q[1] : nullptr;
-    const double *T2 = op.ndim > 2 ? ((mask & 4u) ? d2.Din : d2.Bin) + q[2] : nullptr;
-    const int n1 = op.ndim > 1 ? d1.n_in : 1;
-    const int n2 = op.ndim > 2 ? d2.n_in : 1;
+    int idx[MAXD] = {0};
     double val = 0.0;
-    for (int i0 = 0; i0 < d0.n_in; ++i0)
+    for (int i = 0; i < op.N_in; ++i)
     {
-        const double t0 = T0[i0 * d0.m];
-        for (int i1 = 0; i1 < n1; ++i1)
+        double phi = 1.0;
+        for (int k = 0; k < op.ndim; ++k)
         {
-            const double t01 = T1 ? __dmul_rn(t0, T1[i1 * d1.m]) : t0;
-            for (int i2 = 0; i2 < n2; ++i2)
-            {
-                const double phi = T2 ? __dmul_rn(t01, T2[i2 * d2.m]) : t01;
-                val = __dadd_rn(val, __dmul_rn(phi, dof[(i0 * n1 + i1) * n2 + i2]));
-            }
+            const DimTab &d = op.dim[k];
+            phi = __dmul_rn(phi, (((mask >> k) & 1u) ? d.Din : d.Bin)[idx[k] * d.m + q[k]]);
+        }
+        val = __dadd_rn(val, __dmul_rn(phi, dof[i]));
+        for (int k = op.ndim - 1; k >= 0; --k)
+        {
+            if (++idx[k] < op.dim[k].n_in)
+                break;
+            idx[k] = 0;
         }
     }
     return val;
@@ -199,9 +225,9 @@ __global__ void __launch_bounds__(kThreads)
     {
         const size_t e = t / op.Q;
         const int qf = (int)(t % op.Q);
-        int q[3];
+        int q[MAXD];
         unflatten(qf, op, true, false, q);
-        double jac[9];
+        double jac[IB200_MAX_PHYS * MAXD];
         for (int a = 0; a < n_phys; ++a)
         {
             const double *dof = gdofs + (e * n_phys + a) * op.N_in;
@@ -217,7 +243,7 @@ __global__ void __launch_bounds__(kThreads)
         }
         if (det || jinv || weight_out)
         {
-            double dv, inv[9];
+            double dv, inv[IB200_MAX_PHYS * MAXD];
             qr_det_inverse(n_phys, ndim, jac, &dv, inv);
             if (det)
                 det[t] = dv;
@@ -251,10 +277,37 @@ __global__ void __launch_bounds__(kThreads)
         const int jo = r / op.N_in, ii = r % op.N_in;
         if (symmetric && ii > jo)
             continue;
-        int bo[3], bi[3];
+        int bo[MAXD], bi[MAXD];
         unflatten(jo, op, false, true, bo);
         unflatten(ii, op, false, false, bi);
         const double *wt = weight ? weight + e * op.Q : nullptr;
+        if (op.ndim > 3)
+        {
+            // any dimension count: loop over all quadrature points with an incrementing multi-index
+            int qi[MAXD] = {0};
+            double acc = 0.0;
+            for (int qf = 0; qf < op.Q; ++qf)
+            {
+                double term = wt ? wt[qf] : 1.0;
+                for (int k = 0; k < op.ndim; ++k)
+                {
+                    const DimTab &d = op.dim[k];
+                    const double *Ti = (deriv_in == k ? d.Din : d.Bin) + bi[k] * d.m;
+                    term *= Ti[qi[k]] * d.Bout[bo[k] * d.m + qi[k]] * d.w[qi[k]];
+                }
+                acc += term;
+                for (int k = op.ndim - 1; k >= 0; --k)
+                {
+                    if (++qi[k] < op.dim[k].m)
+                        break;
+                    qi[k] = 0;
+                }
+            }
+            out[t] = acc;
+            if (symmetric && ii != jo)
+                out[e * per_elem + (size_t)ii * op.N_in + jo] = acc;
+            continue;
+        }
         const double *Ti0 = (deriv_in == 0 ? d0.Din : d0.Bin) + bi[0] * d0.m;
         const double *To0 = d0.Bout + bo[0] * d0.m;
         double acc = 0.0;
@@ -311,11 +364,30 @@ __global__ void __launch_bounds__(kThreads)
     for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
     {
         const size_t e = t / op.N_in;
-        int bi[3];
+        int bi[MAXD];
         unflatten((int)(t % op.N_in), op, false, false, bi);
         const double *f = fvals + e * op.Q;
         const double *dt = det ? det + e * op.Q : nullptr;
         double acc = 0.0;
+        if (op.ndim > 3)
+        {
+            int qi[MAXD] = {0};
+            for (int qf = 0; qf < op.Q; ++qf)
+            {
+                double term = dt ? f[qf] * dt[qf] : f[qf];
+                for (int k = 0; k < op.ndim; ++k)
+                    term *= op.dim[k].w[qi[k]] * op.dim[k].Bin[bi[k] * op.dim[k].m + qi[k]];
+                acc += term;
+                for (int k = op.ndim - 1; k >= 0; --k)
+                {
+                    if (++qi[k] < op.dim[k].m)
+                        break;
+                    qi[k] = 0;
+                }
+            }
+            out[t] = acc;
+            continue;
+        }
         for (int q0 = 0; q0 < d0.m; ++q0)
         {
             double a1 = 0.0;

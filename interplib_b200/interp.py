@@ -1,0 +1,690 @@
+"""Drop-in mirror of the reference's per-element API for the hot path (``interplib`` / ``interplib._interp``).
+
+Same names, argument meaning, array shapes and exception types as the reference's CPython extension
+(``/root/reference/src/python/*.c``, stub ``python/interplib/_interp.pyi``) and its NumPy glue
+(``python/interplib/integration.py``, ``degrees_of_freedom.py``); every method cites what it mirrors.
+Nothing is computed in Python: table-only methods call the host C layer of ``libinterp_b200.so``, every
+numeric method is a batch of ONE element through the batched C ABI on the GPU (``interplib_b200.batch``).
+There is no CPU implementation behind the numeric calls -- without a B200 they raise.
+
+The element-batched counterparts (the performance path) are ``interplib_b200.batch.Context`` methods; the
+objects below expose ``.spec`` tuples so the two layers share descriptions.
+"""
+from __future__ import annotations
+
+from enum import StrEnum
+from typing import Callable, Sequence
+
+import numpy as np
+
+from . import batch
+from ._lib import BASIS_TYPES, RULE_TYPES
+
+__all__ = [
+    "BasisType", "IntegrationMethod", "IntegrationRegistry", "IntegrationSpecs", "IntegrationSpace", "BasisRegistry",
+    "BasisSpecs", "FunctionSpace", "DegreesOfFreedom", "CoordinateMap", "SpaceMap", "compute_mass_matrix",
+    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct",
+    "compute_dual_degrees_of_freedom", "DEFAULT_INTEGRATION_REGISTRY", "DEFAULT_BASIS_REGISTRY",
+]
+
+
+class BasisType(StrEnum):
+    """python/interplib/enum_type.py:7-15 (member spellings kept, including the reference's typos)."""
+
+    LEGENDRE = "legendre"
+    BERNSTEIN = "bernstein"
+    LAGRANGE_UNIFORM = "lagrange-uniform"
+    LAGRNAGE_GAUSS = "lagrange-gauss"
+    LAGRNAGE_GAUSS_LOBATTO = "lagrange-gauss-lobatto"
+    LAGRANGE_CHEBYSHEV_GAUSS = "lagrange-chebyshev-gauss"
+
+
+class IntegrationMethod(StrEnum):
+    """python/interplib/enum_type.py:31-35"""
+
+    GAUSS = "gauss"
+    GAUSS_LOBATTO = "gauss-lobatto"
+
+
+def _ctx() -> batch.Context:
+    return batch.default_context()
+
+
+# ------------------------------------------------------------------------------------------------ registries
+class IntegrationRegistry:
+    """Cache of 1-D rules (src/python/integration_objects.c:30-181; C cache src/integration/integration_rules.c:146-341).
+    Host copies of the nodes/weights live here; the device copies live in the GPU context's table cache."""
+
+    def __init__(self, *args, **kwargs):
+        if args or kwargs:
+            raise TypeError("IntegrationRegistry takes no arguments.")
+        self._rules: dict[tuple[str, int], tuple[np.ndarray, np.ndarray]] = {}
+
+    def _get(self, method: str, order: int):
+        key = (method, order)
+        hit = self._rules.get(key)
+        if hit is None:
+            x, w, _ = batch.rule_1d(method, order)
+            x.setflags(write=False)
+            w.setflags(write=False)
+            hit = self._rules[key] = (x, w)
+        return hit
+
+    def usage(self) -> tuple["IntegrationSpecs", ...]:
+        return tuple(IntegrationSpecs(o, m) for m, o in self._rules)
+
+    def clear(self) -> None:
+        self._rules.clear()
+
+
+class BasisRegistry:
+    """Cache of 1-D basis tables keyed by (basis specs, rule specs) (src/python/basis_objects.c:75-240;
+    src/basis/basis_set.c:212-287)."""
+
+    def __init__(self, *args, **kwargs):
+        if args or kwargs:
+            raise TypeError("BasisRegistry takes no arguments.")
+        self._sets: dict[tuple, tuple[np.ndarray, np.ndarray]] = {}
+
+    def _get(self, basis: tuple[str, int], rule: tuple[str, int]):
+        key = (basis, rule)
+        hit = self._sets.get(key)
+        if hit is None:
+            hit = self._sets[key] = batch.basis_table_1d(basis, rule)
+        return hit
+
+    def usage(self) -> tuple[tuple["BasisSpecs", "IntegrationSpecs"], ...]:
+        return tuple((BasisSpecs(bt, bo), IntegrationSpecs(ro, rm)) for (bt, bo), (rm, ro) in self._sets)
+
+    def clear(self) -> None:
+        self._sets.clear()
+
+
+DEFAULT_INTEGRATION_REGISTRY = IntegrationRegistry()
+DEFAULT_BASIS_REGISTRY = BasisRegistry()
+
+
+def _check_registry(reg, cls):
+    if not isinstance(reg, cls):
+        raise TypeError(f"Expected {cls.__name__}, got {type(reg).__name__}")
+    return reg
+
+
+# ------------------------------------------------------------------------------------------------ specs
+class IntegrationSpecs:
+    """src/python/integration_objects.c:213-510: ``IntegrationSpecs(order, /, method="gauss")``."""
+
+    __slots__ = ("_order", "_method")
+
+    def __init__(self, order: int, /, method: str = "gauss"):
+        method = str(method)
+        if method not in RULE_TYPES:
+            raise ValueError(f'Unknown integration method "{method}".')
+        if not isinstance(order, (int, np.integer)) or isinstance(order, bool):
+            raise TypeError("Order must be an integer.")
+        if order < 0:
+            raise ValueError("Order must be a non-negative integer.")
+        self._order, self._method = int(order), method
+
+    order = property(lambda self: self._order)
+    method = property(lambda self: self._method)
+
+    @property
+    def accuracy(self) -> int:
+        """Highest polynomial order integrated exactly (src/integration/integration_rules.c:64-71)."""
+        return batch.rule_1d(self._method, self._order)[2]
+
+    @property
+    def spec(self) -> tuple[str, int]:
+        return (self._method, self._order)
+
+    def nodes(self, registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY) -> np.ndarray:
+        return _check_registry(registry, IntegrationRegistry)._get(self._method, self._order)[0]
+
+    def weights(self, registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY) -> np.ndarray:
+        return _check_registry(registry, IntegrationRegistry)._get(self._method, self._order)[1]
+
+    def __eq__(self, other):
+        return isinstance(other, IntegrationSpecs) and self.spec == other.spec
+
+    def __hash__(self):
+        return hash(self.spec)
+
+    def __repr__(self):
+        return f"IntegrationSpecs({self._order}, {self._method!r})"
+
+
+class BasisSpecs:
+    """src/python/basis_objects.c:243-553: ``BasisSpecs(basis_type, order, /)``."""
+
+    __slots__ = ("_type", "_order")
+
+    def __init__(self, basis_type: str, order: int, /):
+        basis_type = str(basis_type)
+        if basis_type not in BASIS_TYPES:
+            raise ValueError(f"Unknown basis type string: {basis_type}")
+        if order < 0:
+            raise ValueError(f"Order must be positive, but was given as {order}.")
+        self._type, self._order = basis_type, int(order)
+
+    order = property(lambda self: self._order)
+    type = property(lambda self: self._type)  # C name (basis_objects.c:296)
+    basis_type = property(lambda self: self._type)  # name in the typing stub (_interp.pyi:495)
+
+    @property
+    def spec(self) -> tuple[str, int]:
+        return (self._type, self._order)
+
+    def values(self, x, /) -> np.ndarray:
+        """Basis values at arbitrary points -> x.shape + (order+1,) (basis_objects.c:351-428, src/basis/basis_set.c:462-489)."""
+        return batch.basis_at_points(self.spec, np.asarray(x, dtype=np.float64))
+
+    def derivatives(self, x, /) -> np.ndarray:
+        """basis_objects.c:430-491, src/basis/basis_set.c:491-556"""
+        return batch.basis_at_points(self.spec, np.asarray(x, dtype=np.float64), derivative=True)
+
+    def __eq__(self, other):
+        return isinstance(other, BasisSpecs) and self.spec == other.spec
+
+    def __hash__(self):
+        return hash(self.spec)
+
+    def __repr__(self):
+        return f"BasisSpecs({self._type!r}, {self._order})"
+
+
+# ------------------------------------------------------------------------------------------------ spaces
+class IntegrationSpace:
+    """src/python/integration_objects.c:512-876: tensor product of 1-D rules."""
+
+    def __init__(self, *integration_specs: IntegrationSpecs, **kwargs):
+        if kwargs:
+            raise TypeError("Constructor takes no keyword arguments.")
+        if not integration_specs:
+            raise TypeError("Expected at least one argument.")
+        for s in integration_specs:
+            if not isinstance(s, IntegrationSpecs):
+                raise TypeError(f"Expected IntegrationSpecs, got {type(s).__name__}")
+        self._specs = tuple(integration_specs)
+
+    dimension = property(lambda self: len(self._specs))
+    integration_specs = property(lambda self: self._specs)
+    orders = property(lambda self: tuple(s.order for s in self._specs))
+
+    @property
+    def rules(self) -> list[tuple[str, int]]:
+        """``[(method, order), ...]`` -- the description the batched API takes."""
+        return [s.spec for s in self._specs]
+
+    @property
+    def shape(self) -> tuple[int, ...]:
+        return tuple(s.order + 1 for s in self._specs)
+
+    def nodes(self, registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY, /) -> np.ndarray:
+        """[d, m0, m1, ...] (integration_objects.c:731-814)"""
+        _check_registry(registry, IntegrationRegistry)
+        for s in self._specs:
+            registry._get(*s.spec)
+        return batch.integration_space_nodes(self.rules)
+
+    def weights(self, registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY, /) -> np.ndarray:
+        """[m0, m1, ...], product built in ascending dimension order (integration_objects.c:633-716)"""
+        _check_registry(registry, IntegrationRegistry)
+        for s in self._specs:
+            registry._get(*s.spec)
+        return batch.integration_space_weights(self.rules)
+
+    def __eq__(self, other):
+        return isinstance(other, IntegrationSpace) and self._specs == other._specs
+
+    def __hash__(self):
+        return hash(self._specs)
+
+    def __repr__(self):
+        return "IntegrationSpace(" + ", ".join(map(repr, self._specs)) + ")"
+
+
+class FunctionSpace:
+    """src/python/function_space_objects.c:16-636: tensor product of 1-D bases."""
+
+    def __init__(self, *basis_specs: BasisSpecs, **kwargs):
+        if kwargs:
+            raise TypeError("Constructor takes no keyword arguments.")
+        if not basis_specs:
+            raise TypeError("Constructor requires at least one argument.")
+        for i, s in enumerate(basis_specs):
+            if not isinstance(s, BasisSpecs):
+                raise TypeError(f"Argument {i} was not a BasisSpec, but was instead {s!r}.")
+        self._specs = tuple(basis_specs)
+
+    dimension = property(lambda self: len(self._specs))
+    basis_specs = property(lambda self: self._specs)
+    orders = property(lambda self: tuple(s.order for s in self._specs))
+
+    @property
+    def basis(self) -> list[tuple[str, int]]:
+        """``[(type, order), ...]`` -- the description the batched API takes."""
+        return [s.spec for s in self._specs]
+
+    @property
+    def shape(self) -> tuple[int, ...]:
+        return tuple(s.order + 1 for s in self._specs)
+
+    @property
+    def n_basis(self) -> int:
+        return int(np.prod(self.shape))
+
+    def evaluate(self, *x, out: np.ndarray | None = None) -> np.ndarray:
+        """Tensor basis at arbitrary points -> x.shape + (n0, n1, ...) (function_space_objects.c:142-276,
+        src/basis/basis_set.c:577-633)."""
+        if len(x) != self.dimension:
+            raise TypeError("evaluate() takes exactly the same number of positional arguments as the dimension count "
+                            f"({self.dimension}), but {len(x)} were given.")
+        xs = [np.ascontiguousarray(v, dtype=np.float64) for v in x]
+        for v in xs[1:]:
+            if v.shape != xs[0].shape:
+                raise ValueError("All input coordinate arrays must have the same shape.")
+        res = batch.function_space_evaluate(self.basis, xs)
+        if out is not None:
+            if out.shape != res.shape or out.dtype != np.float64 or not out.flags.c_contiguous:
+                raise ValueError("Output array must be a C-contiguous float64 array of shape " + str(res.shape))
+            out[...] = res
+            return out
+        return res
+
+    def values_at_integration_nodes(self, integration: IntegrationSpace, /, *,
+                                    integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                                    basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> np.ndarray:
+        """[m0, .., n0, ..] (function_space_objects.c:301-474)"""
+        if not isinstance(integration, IntegrationSpace):
+            raise TypeError(f"Expected IntegrationSpace, got {type(integration).__name__}")
+        if integration.dimension != self.dimension:
+            raise ValueError("Function space and integration space must have the same number of dimensions (function space "
+                             f"had {self.dimension}, but integration space had {integration.dimension}).")
+        _touch(self, integration, integration_registry, basis_registry)
+        return batch.values_at_integration_nodes(self.basis, integration.rules)
+
+    def lower_order(self, idim: int) -> "FunctionSpace":
+        """function_space_objects.c:490-530"""
+        if idim < 0 or idim >= self.dimension:
+            raise ValueError(f"Dimension {idim} is out of bounds for a function space with {self.dimension} dimensions.")
+        if self._specs[idim].order == 0:
+            raise ValueError(f"Cannot lower order of dimension {idim} as it has order 0.")
+        specs = list(self._specs)
+        specs[idim] = BasisSpecs(specs[idim].type, specs[idim].order - 1)
+        return FunctionSpace(*specs)
+
+    def __eq__(self, other):
+        return isinstance(other, FunctionSpace) and self._specs == other._specs
+
+    def __hash__(self):
+        return hash(self._specs)
+
+    def __repr__(self):
+        return "FunctionSpace(" + ", ".join(map(repr, self._specs)) + ")"
+
+
+def _touch(fs: FunctionSpace, ispace: IntegrationSpace, ireg: IntegrationRegistry, breg: BasisRegistry) -> None:
+    """Record the (basis, rule) pairs a call uses, as the reference's registries would (usage() parity)."""
+    _check_registry(ireg, IntegrationRegistry)
+    _check_registry(breg, BasisRegistry)
+    for b, r in zip(fs.basis_specs, ispace.integration_specs):
+        ireg._get(*r.spec)
+        breg._get(b.spec, r.spec)
+
+
+# ------------------------------------------------------------------------------------------------ DoFs
+class DegreesOfFreedom:
+    """src/python/degrees_of_freedom.c:33-1015: ``DegreesOfFreedom(function_space, values=None, /)``."""
+
+    def __init__(self, function_space: FunctionSpace, values=None, /):
+        if not isinstance(function_space, FunctionSpace):
+            raise TypeError(f"Expected FunctionSpace, got {type(function_space).__name__}")
+        self._fs = function_space
+        self._values = np.zeros(function_space.shape)
+        if values is not None:
+            self.values = values
+
+    function_space = property(lambda self: self._fs)
+    n_dofs = property(lambda self: self._fs.n_basis)
+    shape = property(lambda self: self._fs.shape)
+
+    @property
+    def values(self) -> np.ndarray:
+        return self._values
+
+    @values.setter
+    def values(self, value) -> None:
+        arr = np.asarray(value, dtype=np.float64)
+        if arr.shape != self.shape and arr.shape != (self.n_dofs,):
+            raise ValueError(f"Values must either be flat with {self.n_dofs} elements or have exact correct "
+                             f"{len(self.shape)}-dimensional shape.")
+        self._values[...] = arr.reshape(self.shape)
+
+    def _check_space(self, integration_space: IntegrationSpace, out):
+        if not isinstance(integration_space, IntegrationSpace):
+            raise TypeError(f"Expected IntegrationSpace, got {type(integration_space).__name__}")
+        ndim = self._fs.dimension
+        if integration_space.dimension != ndim:
+            raise ValueError(f"Expected integration space with {ndim} dimensions, but it had only {integration_space.dimension}.")
+        if out is not None:
+            if not isinstance(out, np.ndarray) or out.dtype != np.float64 or not out.flags.c_contiguous:
+                raise ValueError("Output array must be a C-contiguous array of doubles.")
+            if out.ndim != ndim:
+                raise ValueError(f"Output array must have {ndim} dimensions, but it had {out.ndim}.")
+            for k, (m, a) in enumerate(zip(integration_space.shape, out.shape)):
+                if m != a:
+                    raise ValueError("Output array must have the exact same shape as the integration space, but dimension "
+                                     f"{k} did not match (integration space: {m}, array: {a}).")
+
+    def _reconstruct(self, integration_space, mask, ireg, breg, out):
+        self._check_space(integration_space, out)
+        _touch(self._fs, integration_space, ireg, breg)
+        res = _ctx().reconstruct(self._fs.basis, integration_space.rules, self._values.reshape(1, -1), [mask])
+        res = res.reshape(integration_space.shape)
+        if out is not None:
+            out[...] = res
+            return out
+        return res
+
+    def reconstruct_at_integration_points(self, integration_space: IntegrationSpace,
+                                          integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                                          basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY, *, out=None) -> np.ndarray:
+        """[m0, m1, ...] (degrees_of_freedom.c:426-510 -> compute_integration_point_values :232-262): K1, batch of one."""
+        return self._reconstruct(integration_space, 0, integration_registry, basis_registry, out)
+
+    def reconstruct_derivative_at_integration_points(self, integration_space: IntegrationSpace, idim: Sequence[int],
+                                                     integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                                                     basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY, *, out=None) -> np.ndarray:
+        """Derivative along every reference dimension listed in ``idim`` (each at most once)
+        (degrees_of_freedom.c:622-722, index parsing :512-592)."""
+        ndim = self._fs.dimension
+        if isinstance(idim, (int, np.integer)):
+            idim = [int(idim)]
+        mask = 0
+        for i, idx in enumerate(idim):
+            if not isinstance(idx, (int, np.integer)):
+                raise TypeError(f"Expected a sequence of integers, but got a non-integer at index {i}.")
+            if idx < 0 or idx >= ndim:
+                raise ValueError(f"Expected an index between 0 and {ndim - 1}, but got {idx}.")
+            if mask & (1 << idx):
+                raise ValueError(f"Expected each index to appear only once, but got it twice at index {idx}.")
+            mask |= 1 << int(idx)
+        return self._reconstruct(integration_space, mask, integration_registry, basis_registry, out)
+
+
+# ------------------------------------------------------------------------------------------------ geometry
+class CoordinateMap:
+    """One physical coordinate at the integration points: values + d reference gradients, storage [1+d][Q]
+    (src/python/mappings.c:8-280, mappings.h:6-12)."""
+
+    def __init__(self, dofs: DegreesOfFreedom, integration_space: IntegrationSpace,
+                 integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                 basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY, /):
+        if not isinstance(dofs, DegreesOfFreedom):
+            raise TypeError(f"Expected DegreesOfFreedom, got {type(dofs).__name__}")
+        dofs._check_space(integration_space, None)
+        _touch(dofs.function_space, integration_space, integration_registry, basis_registry)
+        self._ispace = integration_space
+        self._dofs = dofs
+        d = integration_space.dimension
+        masks = [0] + [1 << k for k in range(d)]
+        res = _ctx().reconstruct(dofs.function_space.basis, integration_space.rules, dofs.values.reshape(1, -1), masks)
+        self._data = res.reshape((1 + d,) + integration_space.shape)
+        self._data.setflags(write=False)
+
+    dimension = property(lambda self: self._ispace.dimension)
+    integration_space = property(lambda self: self._ispace)
+
+    @property
+    def values(self) -> np.ndarray:
+        return self._data[0]
+
+    def gradient(self, idim: int, /) -> np.ndarray:
+        if idim < 0 or idim >= self.dimension:
+            raise ValueError(f"Expected dimension index in range [0, {self.dimension}), but got {idim}.")
+        return self._data[1 + idim]
+
+
+class SpaceMap:
+    """Reference -> physical map at the integration points: Jacobian, Givens QR, det = prod diag(R), left inverse
+    (src/python/mappings.c:304-787, src/operations/matrices.c:15-141): K0, batch of one."""
+
+    def __init__(self, *coordinates: CoordinateMap, **kwargs):
+        if kwargs:
+            raise TypeError("SpaceMap takes no keyword arguments.")
+        if not coordinates:
+            raise TypeError("SpaceMap requires at least one argument.")
+        for c in coordinates:
+            if not isinstance(c, CoordinateMap):
+                raise TypeError(f"Expected a CoordinateMap, but got a {type(c).__name__}.")
+        first = coordinates[0]
+        ndim, n_phys = first.dimension, len(coordinates)
+        if n_phys < ndim:
+            raise ValueError(f"Can not construct a space map from reference domain with {ndim} dimensions to {n_phys} physical "
+                             "dimensions. The number of physical dimensions must be equal to, or greater than the number of "
+                             "reference dimensions.")
+        for i, c in enumerate(coordinates[1:], 1):
+            if c.dimension != ndim:
+                raise ValueError("Expected all coordinate maps to have the same number of dimensions, but "
+                                 f"got {ndim} and {c.dimension}.")
+            if c.integration_space != first.integration_space:
+                raise ValueError("Expected all coordinate maps to have the same integration space, but the first and "
+                                 f"{i} space have different ones.")
+            if c._dofs.function_space != first._dofs.function_space:
+                # the batched geometry kernel takes one geometry space for all coordinates (the reference's Line/Quad
+                # domains build them that way, python/interplib/domains.py:34-50)
+                raise ValueError("Expected all coordinate maps to use the same function space.")
+        self._coords = tuple(coordinates)
+        self._ispace = first.integration_space
+        geom = np.stack([c._dofs.values.reshape(-1) for c in coordinates])[None]
+        _, det, jinv = _ctx().geometry(first._dofs.function_space.basis, self._ispace.rules, geom, n_phys, want=("det", "jinv"))
+        self._det = det.reshape(self._ispace.shape)
+        self._inv = jinv.reshape(self._ispace.shape + (ndim, n_phys))
+        self._det.setflags(write=False)
+        self._inv.setflags(write=False)
+
+    integration_space = property(lambda self: self._ispace)
+    input_dimensions = property(lambda self: self._ispace.dimension)
+    output_dimensions = property(lambda self: len(self._coords))
+    determinant = property(lambda self: self._det)
+    inverse_map = property(lambda self: self._inv)  # C name (mappings.c:769)
+    inverse_transform = property(lambda self: self._inv)  # name in the typing stub (_interp.pyi:905)
+
+    def coordinate_map(self, idx: int) -> CoordinateMap:
+        if idx < 0 or idx >= len(self._coords):
+            raise ValueError(f"Expected dimension index in range [0, {len(self._coords)}), but got {idx}.")
+        return self._coords[idx]
+
+    @property
+    def geometry_dofs(self) -> np.ndarray:
+        """[n_phys][N_g] coordinate DoFs (what the fused batched kernels take instead of a SpaceMap)."""
+        return np.stack([c._dofs.values.reshape(-1) for c in self._coords])
+
+
+# ------------------------------------------------------------------------------------------------ mass matrices
+def _integration_args(integration):
+    if isinstance(integration, IntegrationSpace):
+        return integration, None
+    if isinstance(integration, SpaceMap):
+        return integration.integration_space, integration
+    raise TypeError(f"Integration space or space map must be passed, instead {type(integration).__name__} object was passed.")
+
+
+def _check_spaces(space_in, space_out, ispace):
+    for s in (space_in, space_out):
+        if not isinstance(s, FunctionSpace):
+            raise TypeError(f"Expected FunctionSpace, got {type(s).__name__}")
+    if space_out.dimension != space_in.dimension or ispace.dimension != space_in.dimension:
+        raise ValueError("Function spaces must have the same dimensionality (space in: "
+                         f"{space_in.dimension}, space out: {space_out.dimension}, integration space: {ispace.dimension}).")
+
+
+def compute_mass_matrix(space_in: FunctionSpace, space_out: FunctionSpace, integration, /, *,
+                        integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                        basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> np.ndarray:
+    """``[N_out, N_in]`` mass matrix on the reference domain (IntegrationSpace) or on the mapped element (SpaceMap)
+    (src/python/mass_matrices.c:161-339): K2, batch of one."""
+    ispace, smap = _integration_args(integration)
+    _check_spaces(space_in, space_out, ispace)
+    _touch(space_in, ispace, integration_registry, basis_registry)
+    _touch(space_out, ispace, integration_registry, basis_registry)
+    weight = None if smap is None else smap.determinant.reshape(1, -1)
+    return _ctx().mass_matrix(space_in.basis, space_out.basis, ispace.rules, 1, weight=weight)[0]
+
+
+def compute_gradient_mass_matrix(space_in: FunctionSpace, space_out: FunctionSpace, integration, /, idim_in: int, idim_out: int, *,
+                                 integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                                 basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> np.ndarray:
+    """Mass matrix with the input basis differentiated along reference dimension ``idim_in`` and weighted by
+    ``det * Jinv[idim_in][idim_out]`` (src/python/mass_matrices.c:341-565)."""
+    ispace, smap = _integration_args(integration)
+    n_coords = ispace.dimension if smap is None else smap.output_dimensions
+    if idim_in < 0 or idim_in >= ispace.dimension:
+        raise ValueError(f"Index {idim_in} out of bounds for input space with {ispace.dimension} dimensions.")
+    if idim_out < 0 or idim_out >= n_coords:
+        raise ValueError(f"Index {idim_out} out of bounds for output space with {n_coords} dimensions.")
+    _check_spaces(space_in, space_out, ispace)
+    if smap is None and idim_in != idim_out:
+        return np.zeros((space_out.n_basis, space_in.n_basis))  # mass_matrices.c:463-474
+    _touch(space_in, ispace, integration_registry, basis_registry)
+    _touch(space_out, ispace, integration_registry, basis_registry)
+    weight = None
+    if smap is not None:
+        weight = (smap.determinant * smap.inverse_map[..., idim_in, idim_out]).reshape(1, -1)  # mass_matrices.c:516-518
+    return _ctx().mass_matrix(space_in.basis, space_out.basis, ispace.rules, 1, weight=weight, deriv_dim_in=idim_in)[0]
+
+
+# ------------------------------------------------------------------------------------------------ NumPy-glue layer
+def _prepare_integration(integration, registry):
+    """python/interplib/integration.py:44-67"""
+    if isinstance(integration, IntegrationSpace):
+        return integration.nodes(registry), None
+    if isinstance(integration, SpaceMap):
+        nodes = np.array([integration.coordinate_map(i).values for i in range(integration.output_dimensions)])
+        return nodes, integration.determinant
+    raise TypeError(f"Only {IntegrationSpace} or {SpaceMap} can be passed, but instead {type(integration)} was passed.")
+
+
+def integrate_callable(func: Callable, integration, /, *, registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY) -> float:
+    """python/interplib/integration.py:70-103"""
+    nodes, det = _prepare_integration(integration, registry)
+    ispace, _ = _integration_args(integration)
+    weights = ispace.weights(registry)
+    if det is not None:
+        weights = weights * det
+    return float(np.sum(np.asarray(func(*[nodes[i, ...] for i in range(nodes.shape[0])])) * weights))
+
+
+def projection_l2_dual(func: Callable, function_space: FunctionSpace, integration, /, *,
+                       integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                       basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> DegreesOfFreedom:
+    """Dual DoFs ``b_i = sum_q f(x_q) W_q det_q phi_i(q)`` (python/interplib/integration.py:106-168): the callable is
+    sampled on the host at the (mapped) nodes, the contraction is K3 on the GPU, batch of one."""
+    nodes, det = _prepare_integration(integration, integration_registry)
+    ispace, _ = _integration_args(integration)
+    if function_space.dimension != ispace.dimension:
+        raise ValueError("Function space and integration space must have the same number of dimensions (function space "
+                         f"had {function_space.dimension}, but integration space had {ispace.dimension}).")
+    fvals = np.broadcast_to(np.asarray(func(*[nodes[i, ...] for i in range(nodes.shape[0])]), dtype=np.float64), ispace.shape)
+    _touch(function_space, ispace, integration_registry, basis_registry)
+    dual = _ctx().l2_dual(function_space.basis, ispace.rules, np.ascontiguousarray(fvals).reshape(1, -1),
+                          det=None if det is None else det.reshape(1, -1))
+    return DegreesOfFreedom(function_space, dual[0])
+
+
+def projection_l2_primal(func: Callable, function_space: FunctionSpace, integration, /, *,
+                         integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                         basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> DegreesOfFreedom:
+    """Primal DoFs ``M u = b`` (python/interplib/integration.py:171-223; the reference calls np.linalg.solve, here the
+    batched Cholesky kernel)."""
+    dual = projection_l2_dual(func, function_space, integration, integration_registry=integration_registry,
+                              basis_registry=basis_registry)
+    mass = compute_mass_matrix(function_space, function_space, integration, integration_registry=integration_registry,
+                               basis_registry=basis_registry)
+    primal = _ctx().spd_solve(mass[None], dual.values.reshape(1, -1))
+    return DegreesOfFreedom(function_space, primal[0])
+
+
+def reconstruct(dof: DegreesOfFreedom, *x) -> np.ndarray:
+    """Function values at arbitrary points (python/interplib/degrees_of_freedom.py:10-37)."""
+    xs = [np.ascontiguousarray(v, dtype=np.float64) for v in x]
+    for v in xs[1:]:
+        if v.shape != xs[0].shape:
+            raise ValueError("All input coordinate arrays must have the same shape.")
+    phi = dof.function_space.evaluate(*xs).reshape((-1, dof.n_dofs))
+    return np.sum(phi * dof.values.flatten(), axis=-1).reshape(xs[0].shape)
+
+
+def compute_dual_degrees_of_freedom(fn: Callable, integration_space: IntegrationSpace, function_space: FunctionSpace, /) -> DegreesOfFreedom:
+    """python/interplib/degrees_of_freedom.py:40-71 (same result as projection_l2_dual on the reference domain)."""
+    return projection_l2_dual(fn, function_space, integration_space)
+
+
+# ------------------------------------------------------------------------------------------------ geometry authoring
+class HypercubeDomain:
+    """An element described by one DoF set per physical coordinate; calling it with an IntegrationSpace builds
+    the SpaceMap (python/interplib/domains.py:28-78).  Only the part of the reference's ``domains`` module that
+    produces the hot path's geometry input is mirrored (straight lines and bilinear quads)."""
+
+    def __init__(self, *dofs: DegreesOfFreedom):
+        if not dofs:
+            raise ValueError("At least one coordinate must have its DoFs specified.")
+        for i, d in enumerate(dofs):
+            if not isinstance(d, DegreesOfFreedom):
+                raise TypeError(f"Argument {i} was not {DegreesOfFreedom}, but {type(d)}.")
+            if d.function_space != dofs[0].function_space:
+                raise ValueError(f"Function spaces of the DoFs {i} does not match the rest!")
+        self.dofs = tuple(dofs)
+
+    ndim_physical = property(lambda self: len(self.dofs))
+    ndim_reference = property(lambda self: len(self.dofs[0].shape))
+    function_space = property(lambda self: self.dofs[0].function_space)
+
+    def __call__(self, space: IntegrationSpace, /, *, integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                 basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> SpaceMap:
+        return SpaceMap(*(CoordinateMap(d, space, integration_registry, basis_registry) for d in self.dofs))
+
+    @property
+    def geometry_dofs(self) -> np.ndarray:
+        """[n_phys][N_g]: one row of the batched API's ``geom_dofs[E][n_phys][N_g]``."""
+        return np.stack([d.values.reshape(-1) for d in self.dofs])
+
+    def sample(self, *x) -> tuple[np.ndarray, ...]:
+        return tuple(reconstruct(d, *x) for d in self.dofs)
+
+
+class Line(HypercubeDomain):
+    """Curve through control points: Bernstein DoFs of order ``len(knots) - 1`` per coordinate
+    (python/interplib/domains.py:200-233)."""
+
+    def __init__(self, *knots):
+        pts = np.array(knots, dtype=np.float64)
+        if pts.ndim != 2:
+            raise ValueError("Line must be specified by an array of points.")
+        if pts.shape[0] < 2:
+            raise ValueError("At least two points must be given for a line.")
+        fs = FunctionSpace(BasisSpecs("bernstein", pts.shape[0] - 1))
+        self.knots = pts
+        super().__init__(*(DegreesOfFreedom(fs, pts[:, k]) for k in range(pts.shape[1])))
+
+    start = property(lambda self: self.knots[0])
+    end = property(lambda self: self.knots[-1])
+
+
+class Quad(HypercubeDomain):
+    """Straight-sided quadrilateral: ``lagrange-uniform`` order-1 DoFs ``[i0][i1]`` per coordinate with the corner at
+    reference position (2*i0-1, 2*i1-1) -- what ``Quad.from_corners`` of the reference produces for linear edges
+    (python/interplib/domains.py:236-331); curved-edge blending is geometry authoring outside the hot path."""
+
+    def __init__(self, *dofs: DegreesOfFreedom):
+        super().__init__(*dofs)
+
+    @classmethod
+    def from_corners(cls, bottom_left, bottom_right, top_right, top_left) -> "Quad":
+        bl, br, tr, tl = (np.asarray(p, dtype=np.float64) for p in (bottom_left, bottom_right, top_right, top_left))
+        fs = FunctionSpace(BasisSpecs("lagrange-uniform", 1), BasisSpecs("lagrange-uniform", 1))
+        return cls(*(DegreesOfFreedom(fs, np.array([[bl[k], tl[k]], [br[k], tr[k]]])) for k in range(bl.shape[0])))
+
+
+__all__ += ["HypercubeDomain", "Line", "Quad"]

@@ -37,7 +37,7 @@
 
 enum
 {
-    ORC_MAX_DIM = 4
+    ORC_MAX_DIM = 6
 };
 enum
 {

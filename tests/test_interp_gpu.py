@@ -1,0 +1,218 @@
+"""GPU half of the drop-in mirror (interplib_b200.interp): the properties the reference's own tests pin
+(tests/test_mass_matrix.py, test_l2_proj.py, test_dofs.py, test_mapping.py, test_gradient.py), restated against the
+mirror.  Every numeric call below is a batch of one element through the C ABI on the B200 -- these tests read like
+the reference's but run the CUDA path."""
+from functools import partial
+
+import numpy as np
+import pytest
+
+from interplib_b200.interp import (BasisSpecs, BasisType, CoordinateMap, DegreesOfFreedom, FunctionSpace, IntegrationSpace,
+                                   IntegrationSpecs, Line, Quad, SpaceMap, compute_dual_degrees_of_freedom,
+                                   compute_gradient_mass_matrix, compute_mass_matrix, integrate_callable, projection_l2_dual,
+                                   projection_l2_primal, reconstruct)
+
+pytestmark = pytest.mark.gpu
+approx = partial(pytest.approx, rel=1e-10, abs=1e-12)  # the reference's tests use rel 1e-6
+
+
+def _space(types_orders):
+    return FunctionSpace(*(BasisSpecs(t, o) for t, o in types_orders))
+
+
+def _gauss(*orders):
+    return IntegrationSpace(*(IntegrationSpecs(o, "gauss") for o in orders))
+
+
+MASS_SPACES = [
+    ([("legendre", 3)], [("legendre", 3)]),
+    ([("lagrange-chebyshev-gauss", 3)], [("legendre", 2)]),
+    ([("legendre", 4)], [("bernstein", 5)]),
+    ([("legendre", 2), ("legendre", 3)], [("legendre", 2), ("legendre", 3)]),
+    ([("legendre", 2), ("bernstein", 3)], [("lagrange-uniform", 2), ("lagrange-gauss-lobatto", 4)]),
+    ([("legendre", 1), ("bernstein", 2), ("lagrange-gauss", 3)], [("legendre", 1), ("bernstein", 2), ("lagrange-gauss", 3)]),
+    ([("legendre", 1), ("bernstein", 2), ("lagrange-gauss", 1)], [("bernstein", 3), ("legendre", 1), ("lagrange-chebyshev-gauss", 2)]),
+]
+
+
+@pytest.mark.parametrize("s_in,s_out", MASS_SPACES)
+def test_mass_matrix_is_the_quadrature_of_basis_products(s_in, s_out):
+    # reference tests/test_mass_matrix.py:16-177 (1-D, 2-D, 3-D; matching and mixed spaces)
+    fs_in, fs_out = _space(s_in), _space(s_out)
+    ispace = _gauss(*(max(a[1], b[1]) + 1 for a, b in zip(s_in, s_out)))
+    M = compute_mass_matrix(fs_in, fs_out, ispace)
+    nodes, w = ispace.nodes(), ispace.weights()
+    pts = [nodes[k] for k in range(nodes.shape[0])]
+    v_in = fs_in.evaluate(*pts).reshape(w.shape + (-1,))
+    v_out = fs_out.evaluate(*pts).reshape(w.shape + (-1,))
+    expected = np.sum(v_in[..., None, :] * v_out[..., :, None] * w[..., None, None], axis=tuple(range(w.ndim)))
+    assert M.shape == (fs_out.n_basis, fs_in.n_basis)
+    assert M == approx(expected)
+    if fs_in == fs_out:
+        assert np.array_equal(M, M.T)  # exact mirror, mass_matrices.c:326-335
+
+
+def test_mass_matrix_argument_errors():
+    fs1, fs2 = _space([("legendre", 2)]), _space([("legendre", 2), ("legendre", 2)])
+    with pytest.raises(ValueError):
+        compute_mass_matrix(fs1, fs2, _gauss(3))
+    with pytest.raises(TypeError):
+        compute_mass_matrix(fs1, fs1, IntegrationSpecs(3))
+    with pytest.raises(ValueError):
+        compute_gradient_mass_matrix(fs1, fs1, _gauss(3), 1, 0)
+    assert not compute_gradient_mass_matrix(fs2, fs2, _gauss(3, 3), 0, 1).any()  # no map, idx_in != idx_out: zeros
+
+
+@pytest.mark.parametrize("order", (1, 2, 4, 10))
+@pytest.mark.parametrize("btype", list(BasisType))
+def test_projection_of_a_member_is_the_identity_1d(order, btype):
+    # reference tests/test_l2_proj.py:20-37
+    fs = _space([(btype, order)])
+    dofs = DegreesOfFreedom(fs, np.random.default_rng(129).random(order + 1))
+    proj = projection_l2_primal(partial(reconstruct, dofs), fs, _gauss(order + 2))
+    assert proj.values == approx(dofs.values, rel=1e-8)
+
+
+@pytest.mark.parametrize("orders", ((1, 1), (2, 4), (10, 4), (1, 1, 1), (2, 4, 6), (6, 4, 3)))
+@pytest.mark.parametrize("types", (("bernstein", "bernstein", "lagrange-gauss"), ("legendre", "lagrange-chebyshev-gauss", "bernstein")))
+def test_projection_of_a_member_is_the_identity_nd(orders, types):
+    # reference tests/test_l2_proj.py:40-91
+    fs = _space(list(zip(types, orders)))
+    dofs = DegreesOfFreedom(fs)
+    dofs.values = np.random.default_rng(129).random(dofs.shape)
+    proj = projection_l2_primal(partial(reconstruct, dofs), fs, _gauss(*(o + 2 for o in orders)))
+    assert proj.values == approx(dofs.values, rel=1e-7)
+
+
+def test_projection_on_a_deformed_surface_in_3d():
+    # reference tests/test_l2_proj.py:94-124: a bilinear quad embedded in 3-D (n_phys = 3 > d = 2, Gram determinant)
+    quad = Quad.from_corners((0, 0, 0), (2, 0, 0.5), (2.2, 1.8, 1.0), (-0.1, 1.5, 0.3))
+    fs = _space([("lagrange-gauss-lobatto", 3), ("legendre", 2)])
+    ispace = _gauss(5, 5)
+    smap = quad(ispace)
+    assert smap.input_dimensions == 2 and smap.output_dimensions == 3 and smap.determinant.shape == (6, 6)
+    dofs = DegreesOfFreedom(fs, np.random.default_rng(3).random((4, 3)))
+    u_q = dofs.reconstruct_at_integration_points(ispace)
+    # the function "u(xi(x))" sampled at the mapped nodes is u_q whatever the map is: project it back
+    proj = projection_l2_primal(lambda *x: u_q, fs, smap)
+    assert proj.values == approx(dofs.values, rel=1e-9)
+    area = integrate_callable(lambda *x: np.ones_like(x[0]), smap)
+    assert area == approx(np.sum(ispace.weights() * smap.determinant))
+
+
+@pytest.mark.parametrize("orders", ((2, 2, 2), (3, 4, 5), (1, 2, 3)))
+def test_dual_dofs_solve_and_reconstruct_polynomials(orders):
+    # reference tests/test_dofs.py:42-71
+    def f(*x):
+        return sum(v**o for v, o in zip(x, orders))
+
+    ispace = _gauss(*(o + 2 for o in orders))
+    fs = _space([("legendre", o) for o in orders])
+    dual = compute_dual_degrees_of_freedom(f, ispace, fs)
+    M = compute_mass_matrix(fs, fs, ispace)
+    dofs = DegreesOfFreedom(fs, np.linalg.solve(M, dual.values.flatten()))
+    pts = np.meshgrid(*[np.linspace(-1, 1, 5)] * len(orders))
+    assert reconstruct(dofs, *pts) == approx(f(*pts), rel=1e-9, abs=1e-11)
+    # the dual DoFs are the NumPy broadcast of integration.py:143-166
+    nodes, w = ispace.nodes(), ispace.weights()
+    phi = fs.values_at_integration_nodes(ispace).reshape(w.size, -1)
+    assert dual.values.flatten() == approx((f(*nodes) * w).reshape(-1) @ phi)
+
+
+@pytest.mark.parametrize("orders", ((2, 2, 2), (3, 4, 5), (1, 2, 3, 2, 1)))
+def test_reconstruction_at_integration_nodes_matches_pointwise_reconstruct(orders):
+    # reference tests/test_dofs.py:74-100 (including the five-dimensional case)
+    ispace = _gauss(*(o + 2 for o in orders))
+    fs = _space([("legendre", o) for o in orders])
+    dofs = DegreesOfFreedom(fs)
+    dofs.values = np.random.default_rng(1234).random(dofs.shape)
+    nodes = ispace.nodes()
+    got = dofs.reconstruct_at_integration_points(ispace)
+    assert got.shape == ispace.shape
+    assert got == approx(reconstruct(dofs, *[nodes[k] for k in range(nodes.shape[0])]))
+    out = np.empty(ispace.shape)
+    assert dofs.reconstruct_at_integration_points(ispace, out=out) is out and np.array_equal(out, got)
+    with pytest.raises(ValueError):
+        dofs.reconstruct_at_integration_points(ispace, out=np.empty(ispace.shape + (1,)))
+    with pytest.raises(ValueError):
+        dofs.reconstruct_derivative_at_integration_points(ispace, idim=[0, 0])
+    with pytest.raises(ValueError):
+        dofs.reconstruct_derivative_at_integration_points(ispace, idim=[len(orders)])
+
+
+@pytest.mark.parametrize("btype", list(BasisType))
+def test_coordinate_map_is_bitwise_the_reconstruction(btype):
+    # reference tests/test_mapping.py:19-151 compares with np.all(==)
+    fs = _space([(btype, 2), (btype, 3), (btype, 1)])
+    ispace = _gauss(3, 2, 4)
+    dofs = DegreesOfFreedom(fs)
+    dofs.values = np.random.default_rng(5).random(dofs.shape)
+    cmap = CoordinateMap(dofs, ispace)
+    assert cmap.dimension == 3 and cmap.integration_space == ispace
+    assert np.array_equal(cmap.values, dofs.reconstruct_at_integration_points(ispace))
+    for k in range(3):
+        assert np.array_equal(cmap.gradient(k), dofs.reconstruct_derivative_at_integration_points(ispace, idim=[k]))
+    with pytest.raises(ValueError):
+        cmap.gradient(3)
+
+
+@pytest.mark.parametrize("n_int", (1, 2, 4))
+@pytest.mark.parametrize("n_b", (2, 4))
+@pytest.mark.parametrize("btype", list(BasisType))
+def test_space_map_determinants(n_int, n_b, btype):
+    # reference tests/test_mapping.py:154-219: 2-D -> 2-D closed-form determinant, 1-D -> 3-D curve length element
+    rng = np.random.default_rng(1 + n_int**2 + n_b * 3)
+    ispace = IntegrationSpace(IntegrationSpecs(n_int + 1), IntegrationSpecs(n_int - 1))
+    fs = _space([(btype, n_b - 1), (btype, n_b + 1)])
+    maps = [CoordinateMap(DegreesOfFreedom(fs, rng.random(fs.shape)), ispace) for _ in range(2)]
+    smap = SpaceMap(*maps)
+    det = maps[0].gradient(0) * maps[1].gradient(1) - maps[0].gradient(1) * maps[1].gradient(0)
+    assert np.abs(smap.determinant) == approx(np.abs(det), rel=1e-9)
+    J = np.stack([np.stack([m.gradient(k) for k in range(2)], axis=-1) for m in maps], axis=-2)  # [q.., phys, ref]
+    eye = np.einsum("...ij,...jk->...ik", smap.inverse_map, J)
+    scale = np.abs(smap.inverse_map).max() * np.abs(J).max()
+    assert np.abs(eye - np.eye(2)).max() < 1e-10 * max(scale, 1.0)
+    # curve in 3-D
+    ispace1 = IntegrationSpace(IntegrationSpecs(n_int))
+    fs1 = _space([(btype, n_b)])
+    maps1 = [CoordinateMap(DegreesOfFreedom(fs1, rng.random(fs1.shape)), ispace1) for _ in range(3)]
+    smap1 = SpaceMap(*maps1)
+    assert smap1.input_dimensions == 1 and smap1.output_dimensions == 3
+    assert np.abs(smap1.determinant) == approx(np.sqrt(sum(m.gradient(0) ** 2 for m in maps1)))
+    with pytest.raises(ValueError):
+        SpaceMap(maps[0])  # 2 reference dimensions cannot map to 1 physical dimension
+    with pytest.raises(ValueError):
+        SpaceMap(maps[0], maps1[0])
+
+
+def test_gradient_mass_matrix_on_a_line_and_an_affine_quad():
+    # reference tests/test_gradient.py:24-49, 97-193: M_grad u = dual DoFs of the analytic physical gradient
+    line = Line((0.5,), (2.0,))
+    fs = _space([("lagrange-gauss-lobatto", 4)])
+    ispace = _gauss(6)
+    smap = line(ispace)
+
+    def f(x):
+        return x**3 - 2 * x
+
+    def dfdx(x):
+        return 3 * x**2 - 2
+
+    u = projection_l2_primal(f, fs, smap)
+    G = compute_gradient_mass_matrix(fs, fs, smap, 0, 0)
+    assert G @ u.values.flatten() == approx(projection_l2_dual(dfdx, fs, smap).values.flatten(), rel=1e-9)
+
+    quad = Quad.from_corners((0, 0), (2, 0.5), (2.5, 2.0), (0.5, 1.5))  # a parallelogram: affine map
+    fs2 = _space([("lagrange-gauss-lobatto", 3), ("legendre", 3)])
+    fs2_out = _space([("lagrange-gauss-lobatto", 2), ("legendre", 3)])
+    isp2 = _gauss(5, 5)
+    smap2 = quad(isp2)
+
+    def g(x, y):
+        return x**2 * y - y**3 + x
+
+    grads = (lambda x, y: 2 * x * y + 1, lambda x, y: x**2 - 3 * y**2)
+    u2 = projection_l2_primal(g, fs2, smap2).values.flatten()
+    for j in range(2):
+        total = sum(compute_gradient_mass_matrix(fs2, fs2_out, smap2, i, j) @ u2 for i in range(2))
+        assert total == approx(projection_l2_dual(grads[j], fs2_out, smap2).values.flatten(), rel=1e-9)
