@@ -246,6 +246,13 @@ IB200_API int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const 
 IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
                                     int where);
 
+/* ---- 8(e): projection norms -------------------------------------------------------------------- */
+/* out[0] = sum_i a[i]*b[i] in FP64 with a fixed (deterministic) reduction tree.  The per-rank partial of the
+ * norms a partitioned projection reports -- sum_e b_e.u_e (= ||Pi f||^2), sum_e sum_q f^2 W det (= ||f||^2, with
+ * a = f*f and b = W*det) -- which the ranks then all-reduce (NCCL).  The reference computes such sums with
+ * np.sum on the host (python/interplib/integration.py:96-103, domains.py:117). */
+IB200_API int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const double *b, double *out, int where);
+
 #ifdef __cplusplus
 }
 #endif

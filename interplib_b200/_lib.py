@@ -121,6 +121,7 @@ _PROTOTYPES = {
          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
     ),
     "ib200_spd_solve_batch": (C.c_int, [C.c_void_p, C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]),
+    "ib200_dot": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
 }
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

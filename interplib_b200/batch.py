@@ -255,6 +255,22 @@ class Context:
         return rhs
 
 
+    # -- norms ---------------------------------------------------------------------------------------
+    def dot(self, a, b, out=None, where=HOST, n=None):
+        """sum_i a[i]*b[i] with a fixed reduction tree (ib200_dot).  Host arrays -> float; device pointers -> the
+        result is left in ``out`` (device pointer to one double)."""
+        if where == HOST:
+            a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1)
+            b = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)
+            if a.size != b.size:
+                raise ValueError("dot: operands differ in size")
+            res = np.zeros(1)
+            check(lib.ib200_dot(self.handle, a.size, _ptr(a), _ptr(b), _ptr(res), HOST))
+            return float(res[0])
+        check(lib.ib200_dot(self.handle, int(n), _ptr(a), _ptr(b), _ptr(out), DEVICE))
+        return out
+
+
 # ---- default context (lazy; one per process) -----------------------------------------------------------
 _default_ctx: Context | None = None
 _default_lock = threading.Lock()

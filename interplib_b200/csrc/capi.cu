@@ -269,6 +269,7 @@ extern "C" int ib200_ctx_destroy(ib200_ctx_t *ctx)
         cudaEventDestroy(ctx->io_event[i]);
     }
     cudaFree(ctx->scratch);
+    cudaFree(ctx->dot_partial);
     for (int i = 0; i < 8; ++i)
         for (int j = 0; j < 2; ++j)
             cudaEventDestroy(ctx->timer[i][j]);
@@ -1042,4 +1043,32 @@ extern "C" int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elem
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
                            return launch_spd_solve(cfg, n, cnt, (double *)dev[0], (double *)dev[1]);
                        });
+}
+
+// ---- projection norms -------------------------------------------------------------------------------------------
+extern "C" int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const double *b, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (!out || (n && (!a || !b)))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "a/b/out must not be NULL");
+    if (where != IB200_DEVICE && where != IB200_HOST)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
+    LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+    if (!ctx->dot_partial)
+        IB_CUDA(cudaMalloc((void **)&ctx->dot_partial, sizeof(double) * (dot_scratch_doubles() + 1)));
+    double *partial = ctx->dot_partial;
+    double *result = partial + dot_scratch_doubles();
+    if (where == IB200_DEVICE)
+        return launch_dot(cfg, n, a, b, partial, out);
+    // host vectors: stage through device scratch (norm vectors are small next to the matrices)
+    void *stage = nullptr;
+    IB_TRY(ctx_scratch(ctx, 2 * n * sizeof(double) + 256, &stage));
+    double *da = (double *)stage, *db = da + n;
+    IB_CUDA(cudaMemcpyAsync(da, a, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    IB_CUDA(cudaMemcpyAsync(db, b, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    IB_TRY(launch_dot(cfg, n, da, db, partial, result));
+    IB_CUDA(cudaMemcpyAsync(out, result, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return INTERP_SUCCESS;
 }

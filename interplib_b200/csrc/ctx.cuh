@@ -105,6 +105,7 @@ struct ib200_ctx
     size_t stage_pin_bytes[3] = {0, 0, 0};
     void *scratch = nullptr;
     size_t scratch_bytes = 0;
+    double *dot_partial = nullptr; // partial sums + result slot of ib200_dot
 };
 
 int ctx_get_table(ib200_ctx *ctx, basis_spec_t b, integration_spec_t r, const DeviceTable **out);
@@ -132,6 +133,8 @@ int launch_mass_generic(const LaunchCfg &cfg, const OpDesc &op, bool symmetric, 
                         int deriv_dim_in, double *out);
 int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *fvals, const double *det, double *out);
 int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs);
+int dot_scratch_doubles();
+int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b, double *partial, double *out);
 
 // Specialised (sum-factorised, templated) 2-D paths: return IB200_ERROR_UNSUPPORTED (without setting the
 // error text) when the shape is outside their instantiation list; the caller then uses the generic kernels.

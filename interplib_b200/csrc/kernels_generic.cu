@@ -471,6 +471,41 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
     }
 }
 
+// ---- projection norms: deterministic two-pass dot product sum_i a[i]*b[i] (fixed block -> partial mapping) ----
+constexpr int kDotBlocks = 592; // 4 CTAs per SM on 148 SMs
+
+__global__ void __launch_bounds__(kThreads) dot_partial_kernel(size_t n, const double *__restrict__ a, const double *__restrict__ b,
+                                                               double *__restrict__ partial)
+{
+    __shared__ double red[kThreads / 32];
+    double acc = 0.0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        acc = fma(a[i], b[i], acc);
+    for (int off = 16; off > 0; off >>= 1)
+        acc += __shfl_down_sync(0xffffffffu, acc, off);
+    if ((threadIdx.x & 31) == 0)
+        red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        double t = 0.0;
+        for (int w = 0; w < kThreads / 32; ++w)
+            t += red[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(32) dot_final_kernel(int n_partial, const double *__restrict__ partial, double *__restrict__ out)
+{
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n_partial; i += 32)
+        acc += partial[i];
+    for (int off = 16; off > 0; off >>= 1)
+        acc += __shfl_down_sync(0xffffffffu, acc, off);
+    if (threadIdx.x == 0)
+        out[0] = acc;
+}
+
 int grid_for(size_t total_threads, int sm_count)
 {
     const size_t blocks = (total_threads + kThreads - 1) / kThreads;
@@ -533,6 +568,21 @@ int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const do
     l2_generic_kernel<<<grid_for(E * op.N_in, cfg.sm_count), kThreads, 0, cfg.stream>>>(op, E, fvals, det, out);
     ++*cfg.launch_counter;
     return check_launch("l2_generic_kernel");
+}
+
+int dot_scratch_doubles()
+{
+    return kDotBlocks;
+}
+
+int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b, double *partial, double *out)
+{
+    dot_partial_kernel<<<kDotBlocks, kThreads, 0, cfg.stream>>>(n, a, b, partial);
+    ++*cfg.launch_counter;
+    IB_TRY(check_launch("dot_partial_kernel"));
+    dot_final_kernel<<<1, 32, 0, cfg.stream>>>(kDotBlocks, partial, out);
+    ++*cfg.launch_counter;
+    return check_launch("dot_final_kernel");
 }
 
 int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs)
