@@ -164,6 +164,9 @@ IB200_API int ib200_ctx_stats(ib200_ctx_t *ctx, unsigned long long *kernel_launc
 IB200_API int ib200_ctx_clear_cache(ib200_ctx_t *ctx);
 /* force the generic (any-dimension, any-order) kernels instead of the specialised ones: testing aid */
 IB200_API int ib200_ctx_set_force_generic(ib200_ctx_t *ctx, int on);
+/* quadrature points per dimension from which the 2-D mass kernels run stage 2 on FP64 DMMA tiles (mma.sync m8n8k4)
+ * instead of DFMA; 0 disables the DMMA kernel.  Default 13, overridable with $IB200_MMA_MIN_POINTS.  Tuning/testing aid. */
+IB200_API int ib200_ctx_set_mma_min_points(ib200_ctx_t *ctx, int points);
 /* host-pointer calls: elements per staged chunk (0 = automatic) */
 IB200_API int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements);
 

@@ -79,6 +79,7 @@ _PROTOTYPES = {
     "ib200_ctx_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_uint)]),
     "ib200_ctx_clear_cache": (C.c_int, [C.c_void_p]),
     "ib200_ctx_set_force_generic": (C.c_int, [C.c_void_p, C.c_int]),
+    "ib200_ctx_set_mma_min_points": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_chunk_elements": (C.c_int, [C.c_void_p, C.c_size_t]),
     "ib200_device_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "ib200_device_free": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -113,6 +113,10 @@ class Context:
     def set_force_generic(self, on: bool) -> None:
         check(lib.ib200_ctx_set_force_generic(self.handle, int(bool(on))))
 
+    def set_mma_min_points(self, points: int) -> None:
+        """Quadrature points per dimension from which the DMMA mass kernel is used (0 = never)."""
+        check(lib.ib200_ctx_set_mma_min_points(self.handle, int(points)))
+
     def set_chunk_elements(self, n: int) -> None:
         check(lib.ib200_ctx_set_chunk_elements(self.handle, int(n)))
 

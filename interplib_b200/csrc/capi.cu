@@ -1,6 +1,7 @@
 // C ABI of libinterp_b200.so (include/interp_b200.h): argument checking, the context with its device table
 // cache, host<->device staging for host-pointer calls, and dispatch to the CUDA kernels.
 #include <algorithm>
+#include <cstdlib>
 #include <string>
 
 #include "ctx.cuh"
@@ -206,6 +207,8 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
     if (!ctx)
         return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "out of host memory");
     ctx->device = device;
+    if (const char *env = std::getenv("IB200_MMA_MIN_POINTS"))
+        ctx->mma_min_points = std::atoi(env) <= 0 ? (1 << 30) : std::atoi(env);
     IB_CUDA(cudaSetDevice(device));
     IB_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
     if (ctx->prop.major < 10)
@@ -324,6 +327,13 @@ extern "C" int ib200_ctx_set_force_generic(ib200_ctx_t *ctx, int on)
 {
     IB_TRY(ctx_check(ctx));
     ctx->force_generic = on != 0;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_mma_min_points(ib200_ctx_t *ctx, int points)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->mma_min_points = points <= 0 ? (1 << 30) : points;
     return INTERP_SUCCESS;
 }
 
@@ -862,6 +872,22 @@ extern "C" int ib200_geometry_batch(ib200_ctx_t *ctx, unsigned ndim, unsigned n_
                        });
 }
 
+// K2 dispatch: DMMA kernel for high orders (>= ctx->mma_min_points quadrature points per dimension), else the DFMA
+// kernel; IB200_ERROR_UNSUPPORTED falls through to the next candidate and finally to the caller's generic kernel.
+static int launch_mass2d_best(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
+                              bool match0, bool match1, int deriv, int wsrc_kind, const OpHost *geom_host, int widx_in, int widx_out,
+                              size_t cnt, const double *wsrc, double *out)
+{
+    if (op.ndim == 2 && op.dim[0].m >= ctx->mma_min_points)
+    {
+        const int res = launch_mass2d_mma(ctx, cfg, key, op, host, match0, match1, deriv, wsrc_kind, geom_host, widx_in, widx_out,
+                                          cnt, wsrc, out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
+    return launch_mass2d_fast(ctx, cfg, key, op, host, match0, match1, deriv, wsrc_kind, geom_host, widx_in, widx_out, cnt, wsrc, out);
+}
+
 // ---- K2 ----------------------------------------------------------------------------------------------------
 extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
                                        const basis_spec_t *basis_out, const integration_spec_t *rules,
@@ -891,7 +917,7 @@ extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
                            if (!cfg.force_generic && cnt)
                            {
-                               const int res = launch_mass2d_fast(ctx, cfg, key, op, host, match0, match1, deriv, weight ? 1 : 0,
+                               const int res = launch_mass2d_best(ctx, cfg, key, op, host, match0, match1, deriv, weight ? 1 : 0,
                                                                   nullptr, -1, 0, cnt, (const double *)dev[0], (double *)dev[1]);
                                if (res != IB200_ERROR_UNSUPPORTED)
                                    return res;
@@ -936,7 +962,7 @@ extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, c
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
                            if (!cfg.force_generic && cnt && fuse_geometry)
                            {
-                               const int res = launch_mass2d_fast(ctx, cfg, key_fused, op, host, match0, match1, deriv, 2, &ghost,
+                               const int res = launch_mass2d_best(ctx, cfg, key_fused, op, host, match0, match1, deriv, 2, &ghost,
                                                                   deriv, idx_out, cnt, (const double *)dev[0], (double *)dev[1]);
                                if (res != IB200_ERROR_UNSUPPORTED)
                                    return res;
@@ -945,7 +971,7 @@ extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, c
                                                           nullptr, (double *)dev[2], deriv, idx_out));
                            if (!cfg.force_generic && cnt)
                            {
-                               const int res = launch_mass2d_fast(ctx, cfg, key_w, op, host, match0, match1, deriv, 1, nullptr, -1,
+                               const int res = launch_mass2d_best(ctx, cfg, key_w, op, host, match0, match1, deriv, 1, nullptr, -1,
                                                                   0, cnt, (const double *)dev[2], (double *)dev[1]);
                                if (res != IB200_ERROR_UNSUPPORTED)
                                    return res;

@@ -97,6 +97,7 @@ struct ib200_ctx
     std::map<std::string, std::shared_ptr<void>> plans; // per-operation kernel plans (kernels_mass2d.cu)
     unsigned long long launches = 0;
     bool force_generic = false;
+    int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
     size_t chunk_elements = 0;
     // staging (host-pointer calls) and scratch (fused generic path)
     void *stage_dev[3] = {nullptr, nullptr, nullptr};
@@ -143,5 +144,8 @@ int launch_eval2d_fast(const LaunchCfg &cfg, const OpDesc &op, const OpHost &hos
 int launch_mass2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                        bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in,
                        int widx_out, size_t E, const double *wsrc, double *out);
+int launch_mass2d_mma(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
+                      bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in,
+                      int widx_out, size_t E, const double *wsrc, double *out);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);
