@@ -32,9 +32,17 @@ sys.path.insert(0, str(ROOT))
 
 from interplib_b200 import synthetic as syn  # noqa: E402
 
-# ncu-measured DRAM traffic per launch of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum from
-# the `ncu --set full` capture summarised under profiles/); None until captured for that workload.
-NCU_TRAFFIC_BYTES = {"c2": None, "c5": None, "c4": None, "c3": None, "c1": None}
+# ncu-measured DRAM traffic of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum of one launch from the
+# `ncu --set full` captures summarised under profiles/*_full.txt) as (bytes per launch, elements in that launch); the
+# bench line scales it to the elements of its own launch.  Slightly below the algorithmic bytes where the tail of the
+# output is still dirty in the 126 MB L2 when the kernel ends.
+NCU_TRAFFIC_BYTES = {
+    "c2": (1969330088, 1 << 20),   # profiles/r01_c2_eval2d_full.txt
+    "c5": (5266912128, 1 << 20),   # profiles/r01_c5_mass2d_full.txt
+    "c4": (5415202552, 1 << 13),   # profiles/r01_c4_mass2d_mma_full.txt
+    "c3": (1301776088, 1 << 15),   # profiles/r01_c3_mass2d_full.txt
+    "c1": None,
+}
 
 
 def peaks():
@@ -439,6 +447,8 @@ def main() -> int:
     kernel_ms = ctx.timer_ms(1) / max(dom_launches, 1)
     achieved = wl.dominant_bytes_per_elem * wl.E / (kernel_ms * 1e-3) / 1e9
     traffic = NCU_TRAFFIC_BYTES.get(args.workload)
+    if traffic is not None:
+        traffic = int(round(traffic[0] * (wl.E / traffic[1])))
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "traffic": traffic, "peak_source": peak_src, "kernel": wl.dominant,
                 "algorithmic_bytes_per_element": wl.dominant_bytes_per_elem, "step_algorithmic_bytes_per_element": wl.bytes_per_elem,
