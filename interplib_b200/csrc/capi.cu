@@ -209,6 +209,8 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
     ctx->device = device;
     if (const char *env = std::getenv("IB200_MMA_MIN_POINTS"))
         ctx->mma_min_points = std::atoi(env) <= 0 ? (1 << 30) : std::atoi(env);
+    if (const char *env = std::getenv("IB200_NO_LO_KERNEL"))
+        ctx->lo_kernel = std::atoi(env) == 0;
     IB_CUDA(cudaSetDevice(device));
     IB_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
     if (ctx->prop.major < 10)
@@ -882,6 +884,12 @@ static int launch_mass2d_best(ib200_ctx *ctx, const LaunchCfg &cfg, const std::s
     {
         const int res = launch_mass2d_mma(ctx, cfg, key, op, host, match0, match1, deriv, wsrc_kind, geom_host, widx_in, widx_out,
                                           cnt, wsrc, out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
+    if (ctx->lo_kernel)
+    {
+        const int res = launch_mass2d_lo(ctx, cfg, key, op, host, match0, match1, deriv, wsrc_kind, geom_host, widx_in, cnt, wsrc, out);
         if (res != IB200_ERROR_UNSUPPORTED)
             return res;
     }

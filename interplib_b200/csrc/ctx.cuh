@@ -98,6 +98,7 @@ struct ib200_ctx
     unsigned long long launches = 0;
     bool force_generic = false;
     int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
+    bool lo_kernel = true;   // compile-time specialised low-order mass kernel (IB200_NO_LO_KERNEL=1 disables it)
     size_t chunk_elements = 0;
     // staging (host-pointer calls) and scratch (fused generic path)
     void *stage_dev[3] = {nullptr, nullptr, nullptr};
@@ -147,5 +148,8 @@ int launch_mass2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
 int launch_mass2d_mma(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                       bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in,
                       int widx_out, size_t E, const double *wsrc, double *out);
+int launch_mass2d_lo(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
+                     bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in, size_t E,
+                     const double *wsrc, double *out);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);
