@@ -99,7 +99,8 @@ class Workload:
             self.h_in = {"geom": geom, "fvals": rng.standard_normal((E, Q))}
             self.out_shapes = {"mass": (E, N, N), "rhs": (E, N)}
             self.bytes_per_elem = 8 * (geom[0].size + Q + N * N + N)
-            self.dominant = "mass2d_kernel (K2, geometry fused)" if cfg.ndim == 2 else "geometry + mass kernels (1-D generic)"
+            self.dominant = ({"c5": "mass2d_lo_kernel (K2-lo, geometry fused)", "c4": "mass2d_mma_kernel (K2-hi DMMA, geometry fused)"}
+                             .get(name, "mass2d_kernel (K2, geometry fused)") if cfg.ndim == 2 else "geometry + mass kernels (1-D generic)")
             self.dominant_bytes_per_elem = 8 * (geom[0].size + N * N)
             self.metric = "element_mass_matrices_per_s"
             self.unit = "elements/s"
@@ -123,12 +124,14 @@ class Workload:
                 c.mass_matrix_mapped(sb, sa, self.rules, self.gb, self.d_in["geom"].ptr, 2, out=self.d_out[f"block_{a}{b}"].ptr,
                                      where=DEVICE, n_elements=self.E)
         else:
-            c.mass_matrix_mapped(self.basis, self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys,
-                                 out=self.d_out["mass"].ptr, where=DEVICE, n_elements=self.E)
             if dominant_only:
+                c.mass_matrix_mapped(self.basis, self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys,
+                                     out=self.d_out["mass"].ptr, where=DEVICE, n_elements=self.E)
                 return
-            c.l2_dual_mapped(self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys, self.d_in["fvals"].ptr,
-                             out=self.d_out["rhs"].ptr, where=DEVICE, n_elements=self.E)
+            # mass matrix + L2 right-hand side of the same elements: one fused kernel at low order (K2-lo + K3),
+            # two launches otherwise (ib200_l2_system_mapped_batch)
+            c.l2_system_mapped(self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys, self.d_in["fvals"].ptr,
+                               mass=self.d_out["mass"].ptr, rhs=self.d_out["rhs"].ptr, where=DEVICE, n_elements=self.E)
 
     # end to end through the public host-pointer API (pinned host buffers, H2D + D2H inside the call)
     def e2e_prepare(self) -> None:
@@ -147,10 +150,8 @@ class Workload:
             for a, b, sa, sb in self.blocks:
                 c.mass_matrix_mapped(sb, sa, self.rules, self.gb, self.p_in["geom"].array, 2, out=self.p_out[f"block_{a}{b}"].array)
             return float(self.p_out["block_11"].array[-1, 0, 0])
-        c.mass_matrix_mapped(self.basis, self.basis, self.rules, self.gb, self.p_in["geom"].array, self.cfg.n_phys,
-                             out=self.p_out["mass"].array)
-        c.l2_dual_mapped(self.basis, self.rules, self.gb, self.p_in["geom"].array, self.cfg.n_phys, self.p_in["fvals"].array,
-                         out=self.p_out["rhs"].array)
+        c.l2_system_mapped(self.basis, self.rules, self.gb, self.p_in["geom"].array, self.cfg.n_phys, self.p_in["fvals"].array,
+                           mass=self.p_out["mass"].array, rhs=self.p_out["rhs"].array)
         return float(self.p_out["rhs"].array[-1, 0])
 
     @property

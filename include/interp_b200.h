@@ -167,6 +167,9 @@ IB200_API int ib200_ctx_set_force_generic(ib200_ctx_t *ctx, int on);
 /* quadrature points per dimension from which the 2-D mass kernels run stage 2 on FP64 DMMA tiles (mma.sync m8n8k4)
  * instead of DFMA; 0 disables the DMMA kernel.  Default 13, overridable with $IB200_MMA_MIN_POINTS.  Tuning/testing aid. */
 IB200_API int ib200_ctx_set_mma_min_points(ib200_ctx_t *ctx, int points);
+/* compile-time specialised low-order mass kernel (kernels_mass2d_lo.cu) on/off; default on, $IB200_NO_LO_KERNEL=1
+ * turns it off.  Tuning/testing aid: with it off the run-time-shaped kernel serves the same shapes. */
+IB200_API int ib200_ctx_set_lo_kernel(ib200_ctx_t *ctx, int on);
 /* host-pointer calls: elements per staged chunk (0 = automatic) */
 IB200_API int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements);
 
@@ -241,6 +244,18 @@ IB200_API int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const 
                                          const integration_spec_t *rules, unsigned n_phys,
                                          const basis_spec_t *geom_basis, size_t n_elements,
                                          const double *geom_dofs, const double *fvals, double *out, int where);
+
+/* K2 + K3 in one pass: the pair (M, b) that projection_l2_primal assembles per element
+ * (python/interplib/integration.py:171-223: compute_mass_matrix(space, space, smap) and
+ * projection_l2_dual(...)): mass[E][N][N] and rhs[E][N] from geom_dofs[E][n_phys][N_g] and
+ * fvals[E][Q].  Low-order bilinear quads take ONE fused kernel (geometry, mass matrix and
+ * right-hand side share the determinant); every other shape runs the two operations back to
+ * back.  Results are bit-identical to the separate calls. */
+IB200_API int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                           const integration_spec_t *rules, unsigned n_phys,
+                                           const basis_spec_t *geom_basis, size_t n_elements,
+                                           const double *geom_dofs, const double *fvals, double *mass,
+                                           double *rhs, int where);
 
 /* ---- N1 ("next"): batched primal solve M u = b --------------------------------- */
 /* projection_l2_primal, python/interplib/integration.py:171-223 (np.linalg.solve per element).

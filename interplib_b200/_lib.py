@@ -80,6 +80,7 @@ _PROTOTYPES = {
     "ib200_ctx_clear_cache": (C.c_int, [C.c_void_p]),
     "ib200_ctx_set_force_generic": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_mma_min_points": (C.c_int, [C.c_void_p, C.c_int]),
+    "ib200_ctx_set_lo_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_chunk_elements": (C.c_int, [C.c_void_p, C.c_size_t]),
     "ib200_device_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "ib200_device_free": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -120,6 +121,11 @@ _PROTOTYPES = {
         C.c_int,
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
+    ),
+    "ib200_l2_system_mapped_batch": (
+        C.c_int,
+        [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
+         C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
     ),
     "ib200_spd_solve_batch": (C.c_int, [C.c_void_p, C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]),
     "ib200_dot": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),

@@ -117,6 +117,10 @@ class Context:
         """Quadrature points per dimension from which the DMMA mass kernel is used (0 = never)."""
         check(lib.ib200_ctx_set_mma_min_points(self.handle, int(points)))
 
+    def set_lo_kernel(self, on: bool) -> None:
+        """Compile-time specialised low-order mass kernel on/off (testing aid)."""
+        check(lib.ib200_ctx_set_lo_kernel(self.handle, int(bool(on))))
+
     def set_chunk_elements(self, n: int) -> None:
         check(lib.ib200_ctx_set_chunk_elements(self.handle, int(n)))
 
@@ -245,6 +249,25 @@ class Context:
         check(lib.ib200_l2_dual_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
                                              basis_specs(geom_basis), E, _ptr(geom_dofs), _ptr(fvals), _ptr(out), where))
         return out
+
+    def l2_system_mapped(self, basis, rules, geom_basis, geom_dofs, n_phys, fvals, mass=None, rhs=None, where=HOST,
+                         n_elements=None):
+        """K2 + K3 in one pass: (mass[E][N][N], rhs[E][N]) of the L2 projection   (ib200_l2_system_mapped_batch)"""
+        N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if where == HOST:
+            fvals = _as_in(fvals, (-1, Q))
+            E = fvals.shape[0]
+            geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
+            if mass is None:
+                mass = np.empty((E, N, N))
+            if rhs is None:
+                rhs = np.empty((E, N))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_l2_system_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
+                                               basis_specs(geom_basis), E, _ptr(geom_dofs), _ptr(fvals), _ptr(mass), _ptr(rhs),
+                                               where))
+        return mass, rhs
 
     # -- N1 ----------------------------------------------------------------------------------------
     def spd_solve(self, mass, rhs, where=HOST, n=None, n_elements=None):

@@ -339,6 +339,13 @@ extern "C" int ib200_ctx_set_mma_min_points(ib200_ctx_t *ctx, int points)
     return INTERP_SUCCESS;
 }
 
+extern "C" int ib200_ctx_set_lo_kernel(ib200_ctx_t *ctx, int on)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->lo_kernel = on != 0;
+    return INTERP_SUCCESS;
+}
+
 extern "C" int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements)
 {
     IB_TRY(ctx_check(ctx));
@@ -1059,6 +1066,71 @@ extern "C" int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const
                            }
                            return launch_l2_generic(cfg, op, cnt, (const double *)dev[1], (const double *)dev[3],
                                                     (double *)dev[2]);
+                       });
+}
+
+// ---- K2 + K3 fused ------------------------------------------------------------------------------------------
+extern "C" int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                            const integration_spec_t *rules, unsigned n_phys,
+                                            const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                            const double *fvals, double *mass, double *rhs, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    IB_TRY(check_geometry_dims(ndim, n_phys));
+    if (!basis || !geom_basis)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/geom_basis must not be NULL");
+    if (n_elements && (!fvals || !mass || !rhs || !geom_dofs))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/fvals/mass/rhs must not be NULL");
+    OpDesc op, gop;
+    OpHost host, ghost;
+    IB_TRY(ctx_make_op(ctx, ndim, basis, basis, rules, &op, &host));
+    IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
+    const bool fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
+    const std::string key_fused = plan_key("massg", ndim, basis, basis, rules, geom_basis, -1, 2, -1, 0);
+    const std::string key_w = plan_key("mass", ndim, basis, basis, rules, nullptr, -1, 1, -1, 0);
+    const std::string key_l2 = plan_key("l2g", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
+    const std::string key_l2w = plan_key("l2", ndim, basis, nullptr, rules, nullptr, 1, 0, 0, 0);
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
+                                      {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
+                                      {ARR_OUT, mass, sizeof(double) * op.N_out * op.N_in},
+                                      {ARR_OUT, rhs, sizeof(double) * op.N_in},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
+    return run_batched(ctx, n_elements, arrays, where, 0,
+                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                           const double *g = (const double *)dev[0], *f = (const double *)dev[1];
+                           double *M = (double *)dev[2], *b = (double *)dev[3], *w = (double *)dev[4];
+                           if (!cnt)
+                               return INTERP_SUCCESS;
+                           if (!cfg.force_generic && fuse_geometry)
+                           {
+                               if (ctx->lo_kernel)
+                               {
+                                   // one launch: geometry + mass matrix + right-hand side
+                                   const int res = launch_mass2d_lo(ctx, cfg, key_fused, op, host, true, true, -1, 2, &ghost, -1, cnt,
+                                                                    g, M, f, b);
+                                   if (res != IB200_ERROR_UNSUPPORTED)
+                                       return res;
+                               }
+                               int res = launch_mass2d_best(ctx, cfg, key_fused, op, host, true, true, -1, 2, &ghost, -1, 0, cnt, g, M);
+                               if (res == INTERP_SUCCESS)
+                                   res = launch_l2dual2d_fast(ctx, cfg, key_l2, op, host, 2, &ghost, cnt, f, g, b);
+                               if (res != IB200_ERROR_UNSUPPORTED)
+                                   return res;
+                           }
+                           IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, g, nullptr, nullptr, nullptr, w, -1, 0));
+                           int res = IB200_ERROR_UNSUPPORTED;
+                           if (!cfg.force_generic)
+                               res = launch_mass2d_best(ctx, cfg, key_w, op, host, true, true, -1, 1, nullptr, -1, 0, cnt, w, M);
+                           if (res == IB200_ERROR_UNSUPPORTED)
+                               res = launch_mass_generic(cfg, op, true, cnt, w, -1, M);
+                           IB_TRY(res);
+                           res = IB200_ERROR_UNSUPPORTED;
+                           if (!cfg.force_generic)
+                               res = launch_l2dual2d_fast(ctx, cfg, key_l2w, op, host, 1, nullptr, cnt, f, w, b);
+                           if (res == IB200_ERROR_UNSUPPORTED)
+                               res = launch_l2_generic(cfg, op, cnt, f, w, b);
+                           return res;
                        });
 }
 

@@ -150,6 +150,6 @@ int launch_mass2d_mma(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &k
                       int widx_out, size_t E, const double *wsrc, double *out);
 int launch_mass2d_lo(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                      bool match0, bool match1, int deriv_dim_in, int wsrc_kind, const OpHost *geom_host, int widx_in, size_t E,
-                     const double *wsrc, double *out);
+                     const double *wsrc, double *out, const double *fvals = nullptr, double *rhs = nullptr);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);

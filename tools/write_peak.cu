@@ -123,9 +123,9 @@ int main()
         ms = time_ms([&] { cudaMemcpyAsync(out, in, bytes, cudaMemcpyDeviceToDevice); });
         printf(", \"memcpy_d2d_rw_gbs\": %.1f", 2.0 * bytes / ms / 1e6);
     }
-    for (int kb : {4, 8, 16, 32})
+    for (int kb4 : {4, 8, 16, 32, 64, 128}) // quarter-KB units: 1, 2, 4, 8, 16, 32 KB
     {
-        const int chunk_doubles = kb * 128;
+        const int chunk_doubles = kb4 * 32;
         const size_t n_chunks = n / chunk_doubles;
         for (int nbuf : {1, 2})
         {
@@ -145,8 +145,19 @@ int main()
                 CK(cudaFuncSetAttribute(tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 ms = time_ms([&] { tma_kernel<2><<<sms * per_sm, 256, smem>>>(out, n_chunks, chunk_doubles); });
             }
-            printf(", \"tma_%dkb_nbuf%d_cta%d_gbs\": %.1f", kb, nbuf, per_sm, bytes / ms / 1e6);
+            printf(", \"tma_%dB_nbuf%d_cta%d_gbs\": %.1f", chunk_doubles * 8, nbuf, per_sm, bytes / ms / 1e6);
         }
+    }
+    // chunks whose ends are 16-byte but not 32-byte (sector) aligned, like the row panels of odd-sized element matrices
+    for (int chunk_doubles : {250, 626, 2500})
+    {
+        const size_t n_chunks = n / chunk_doubles;
+        const size_t smem = (size_t)8 * chunk_doubles * 8;
+        int per_sm = (int)((220 * 1024) / smem);
+        per_sm = per_sm > 8 ? 8 : per_sm;
+        CK(cudaFuncSetAttribute(tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        float ms = time_ms([&] { tma_kernel<1><<<sms * per_sm, 256, smem>>>(out, n_chunks, chunk_doubles); });
+        printf(", \"tma_%dB_unaligned_nbuf1_cta%d_gbs\": %.1f", chunk_doubles * 8, per_sm, (double)n_chunks * chunk_doubles * 8 / ms / 1e6);
     }
     printf("}\n");
     CK(cudaDeviceSynchronize());
