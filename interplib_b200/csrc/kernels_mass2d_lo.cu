@@ -57,19 +57,6 @@ __device__ __forceinline__ void lo_fence_async_smem()
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-__device__ __forceinline__ void lo_cp_async8(double *sdst, const double *gsrc)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(lo_smem_u32(sdst)), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void lo_cp_async_commit()
-{
-    asm volatile("cp.async.commit_group;" ::: "memory");
-}
-__device__ __forceinline__ void lo_cp_async_wait_all()
-{
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-}
-
 // TILE = true: the whole matrices of the warp's EPW elements are staged back to back and leave as ONE bulk copy (a
 // warp tile is one contiguous run of global memory).  Used for odd N, where the row panels of an element start and end
 // in the middle of 32-byte sectors: bulk stores of 2 000 B with sector-unaligned ends reach 5.58 TB/s, 20 000 B ones
@@ -95,7 +82,7 @@ struct LoShape
     static constexpr int WARPS = TILE ? 3 : 4;
     static_assert(!TILE || (EPW % 2 == 0), "tile mode needs 16-byte aligned tile starts");
     static constexpr int SLOTS = R * TPE;                 // column-pair slots per element (>= NB)
-    // per warp: W[EPW][Qp] | prefetched inputs x2 (run-time size, LoParams::in_doubles) | panels NBUF*EPW*cap
+    // per warp: W[EPW][Qp] | parked inputs (run-time size, LoParams::in_doubles) | panels NBUF*EPW*cap
 };
 
 template <int N, int M>
@@ -106,7 +93,7 @@ struct LoParams
     double Bw0[N][M], Bw1[N][M];   // basis value * rule weight per dimension (fused right-hand side)
     int wsrc;                      // 0: unit weights, 1: weight[E][Q], 2: bilinear geometry [E][2][2][2] -> det
     int aux_per;                   // prefetched doubles per element of the weight source: 0, Q or 8
-    int in_doubles;                // doubles of one prefetch buffer: EPW * (aux_per + (rhs ? Q : 0)), even
+    int in_doubles;                // doubles of the per-warp input buffer: EPW * (aux_per + (rhs ? Q : 0)), even
     int cap;                       // staged doubles per element and panel (CAP0 + bank skew, even)
 };
 
@@ -127,9 +114,9 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
     // CTA-shared: element-independent geometry products per point, pt[q][0..3] = dphi0[i0]*phi1[i1] (d/dxi0),
     // pt[q][4..7] = phi0[i0]*dphi1[i1] (d/dxi1), rounded like the reference's basis product
     double *pt = smem;
-    double *Wsm = smem + 8 * S::Q + (size_t)warp * (S::EPW * S::Qp + 2 * prm.in_doubles + S::NBUF * S::EPW * prm.cap);
+    double *Wsm = smem + 8 * S::Q + (size_t)warp * (S::EPW * S::Qp + prm.in_doubles + S::NBUF * S::EPW * prm.cap);
     double *Insm = Wsm + S::EPW * S::Qp;
-    double *stage = Insm + 2 * prm.in_doubles;
+    double *stage = Insm + prm.in_doubles;
     const bool want_rhs = rhs != nullptr;
     if (prm.wsrc == 2)
     {
@@ -163,44 +150,57 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
     const size_t n_warps = (size_t)gridDim.x * S::WARPS;
     unsigned pc = 0; // running panel counter of this warp
 
-    // The tile's inputs (8 corner coordinates or Q weights per element, and the Q sampled values) are copied to
-    // per-warp shared memory one tile ahead with cp.async, so their global-memory latency hides behind stages 1 and 2.
-    auto prefetch = [&](size_t t, int b) {
-        if (t >= n_tiles)
-            return;
+    // The tile's inputs (8 corner coordinates or Q weights per element, and the Q sampled values) are loaded into
+    // registers one tile ahead (lane-strided, coalesced) and parked in per-warp shared memory at the top of their tile,
+    // so their global-memory latency hides behind stages 1 and 2.  (Not cp.async: its wait shares the scoreboard of
+    // cp.async.bulk.wait_group.read in SASS -- DEPBAR.LE SB0 -- and would serialise the tile behind its predecessor's
+    // bulk store; measured with ncu, 36 % of the stall samples.)
+    constexpr int NPF = (S::EPW * S::Q + 31) / 32;
+    constexpr int NPA = NPF > (S::EPW * 8 + 31) / 32 ? NPF : (S::EPW * 8 + 31) / 32;
+    double pre_aux[NPA], pre_f[NPF];
+    auto prefetch = [&](size_t t) {
         const size_t e0 = t * S::EPW;
-        const int nv = (int)((E - e0) < (size_t)S::EPW ? (E - e0) : (size_t)S::EPW);
-        double *dst = Insm + b * prm.in_doubles;
+        const int nv = t < n_tiles ? (int)((E - e0) < (size_t)S::EPW ? (E - e0) : (size_t)S::EPW) : 0;
         const int per = prm.aux_per;
         const double *src = wsrc + e0 * per;
-        for (int i = lane; i < nv * per; i += 32)
-            lo_cp_async8(dst + i, src + i);
+#pragma unroll
+        for (int k = 0; k < NPA; ++k)
+            pre_aux[k] = (lane + 32 * k < nv * per) ? src[lane + 32 * k] : 0.0;
         if (want_rhs)
         {
             const double *fsrc = fvals + e0 * S::Q;
-            for (int i = lane; i < nv * S::Q; i += 32)
-                lo_cp_async8(dst + S::EPW * per + i, fsrc + i);
+#pragma unroll
+            for (int k = 0; k < NPF; ++k)
+                pre_f[k] = (lane + 32 * k < nv * S::Q) ? fsrc[lane + 32 * k] : 0.0;
         }
     };
-    int ibuf = 0;
-    prefetch((size_t)blockIdx.x * S::WARPS + warp, 0);
-    lo_cp_async_commit();
+    prefetch((size_t)blockIdx.x * S::WARPS + warp);
 
-    for (size_t tile = (size_t)blockIdx.x * S::WARPS + warp; tile < n_tiles; tile += n_warps, ibuf ^= 1)
+    for (size_t tile = (size_t)blockIdx.x * S::WARPS + warp; tile < n_tiles; tile += n_warps)
     {
         const size_t e = tile * S::EPW + el;
         const bool el_valid = lane_active && e < E;
 
         // ---- per-point weights of the tile's elements -> shared memory (per warp)
-        lo_cp_async_wait_all();
-        __syncwarp(); // this tile's inputs have landed; stage-1 readers of the previous tile are done
-        prefetch(tile + n_warps, ibuf ^ 1);
-        lo_cp_async_commit();
+        __syncwarp(); // readers of the previous tile's inputs and weights are done
+#pragma unroll
+        for (int k = 0; k < NPA; ++k)
+            if (lane + 32 * k < S::EPW * prm.aux_per)
+                Insm[lane + 32 * k] = pre_aux[k];
+        if (want_rhs)
+        {
+#pragma unroll
+            for (int k = 0; k < NPF; ++k)
+                if (lane + 32 * k < S::EPW * S::Q)
+                    Insm[S::EPW * prm.aux_per + lane + 32 * k] = pre_f[k];
+        }
+        __syncwarp();
+        prefetch(tile + n_warps);
         if (el_valid)
         {
             double *W = Wsm + el * S::Qp;
-            const double *in_aux = Insm + ibuf * prm.in_doubles;
-            double *G = Insm + ibuf * prm.in_doubles + S::EPW * prm.aux_per + el * S::Q; // f in, f*W out (in place)
+            const double *in_aux = Insm;
+            double *G = Insm + S::EPW * prm.aux_per + el * S::Q; // f in, f*W out (in place)
             const double *in_f = G;
             if (prm.wsrc == 2)
             {
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
         // same operation order as l2dual2d_kernel, so the fused and the separate results are bit-identical
         if (want_rhs && el_valid)
         {
-            const double *G = Insm + ibuf * prm.in_doubles + S::EPW * prm.aux_per + el * S::Q;
+            const double *G = Insm + S::EPW * prm.aux_per + el * S::Q;
             for (int i1 = bg; i1 < N; i1 += S::TPE)
             {
                 double bw1[M], sv[M];
@@ -562,7 +562,7 @@ int launch_lo(const LaunchCfg &cfg, LoPlan &plan, const OpHost &host, int wsrc_k
     prm.in_doubles = (S::EPW * (prm.aux_per + (rhs ? S::Q : 0)) + 1) & ~1;
     prm.cap = plan.cap;
     const size_t smem_bytes =
-        sizeof(double) * (8 * S::Q + (size_t)S::WARPS * (S::EPW * S::Qp + 2 * prm.in_doubles + S::NBUF * S::EPW * prm.cap));
+        sizeof(double) * (8 * S::Q + (size_t)S::WARPS * (S::EPW * S::Qp + prm.in_doubles + S::NBUF * S::EPW * prm.cap));
     if (wsrc_kind == 2)
     {
         std::memcpy(prm.gB0, geom_host->Bin[0], sizeof(double) * 2 * M);
