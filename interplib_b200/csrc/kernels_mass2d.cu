@@ -26,6 +26,7 @@
 // Exact symmetry of the result for matching spaces needs no mirroring pass: M[J][I] and M[I][J] are produced by
 // the same DFMA sequence on bitwise-identical operands.
 #include <algorithm>
+#include <cstdlib>
 #include <memory>
 #include <string>
 
@@ -109,13 +110,16 @@ __device__ __forceinline__ double bilinear_ref_order(const double t0[2], const d
     return val;
 }
 
-constexpr int min_blocks_for(int M, int R)
+// Resident CTAs the register allocation is sized for.  The kernel is latency-bound at 8 warps per SM (ncu: issue slots
+// 41 % busy, stall reason "wait"), so up to 10 points per dimension the registers are capped at 128 for two 256-thread
+// CTAs per SM (a few hundred bytes of spills at R = 3, M = 10; net +25..40 % on the C3 blocks).
+constexpr int min_blocks_for(int M, int R, bool /*symb*/)
 {
-    return (M <= 6 && R == 2) ? 3 : ((M <= 10 && R == 2) || M <= 6 ? 2 : 1);
+    return (M <= 6 && R == 2) ? 3 : (M <= 10 ? 2 : 1);
 }
 
 template <int M, int R, bool SYMB, int CAP>
-__global__ void __launch_bounds__(256, min_blocks_for(M, R))
+__global__ void __launch_bounds__(256, min_blocks_for(M, R, SYMB))
     mass2d_kernel(const __grid_constant__ MassParams<CAP> prm, const double *__restrict__ P1g, const int2 *__restrict__ bmap,
                   const double *__restrict__ gtab, size_t E, const double *__restrict__ wsrc, double *__restrict__ out)
 {
@@ -469,43 +473,54 @@ static int build_plan(const OpDesc &op, const OpHost &host, bool match0, bool ma
     s.widx_in = widx_in;
     s.widx_out = widx_out;
     s.Qp = (M * M + 1) & ~1;
-    // thread mapping: R items per thread, choose the R with the better lane utilisation (ties -> larger R)
-    int best_R = 0;
+    // thread mapping: R items per thread, an engine of G warps hosts EPE = floor(32 G / BGp) elements; choose (R, G)
+    // for lane utilisation NB*EPE / (R*32*G) (e.g. NB = 72, R = 3: 24 threads per element -> 3 warps host 4 elements
+    // with every lane busy, one warp alone would idle 8 of 32).  Ties: fewer warps per engine, then the larger R
+    // from 9 points per dimension (it amortises the coefficient loads; below that it costs registers).
+    const int row_block = n_out1 * s.N_in;
+    int best_R = 0, best_G = 0;
     double best_util = -1.0;
     for (int R = 2; R <= 3; ++R)
     {
         const int bgp = (s.NB + R - 1) / R;
-        const int G = bgp <= 32 ? 1 : (bgp + 31) / 32;
-        if (G > 4)
-            continue;
-        const int epe = G == 1 ? 32 / bgp : 1;
-        const double util = (double)s.NB * epe / (double)(R * 32 * G);
-        // ties: the wider item set amortises the uniform coefficient loads better, but below ~9 points per
-        // dimension it costs a resident CTA (registers), so prefer R = 2 there
-        const bool better = util > best_util + 1e-9 || (util >= best_util - 1e-9 && M >= 9);
-        if (better)
+        for (int G = (bgp + 31) / 32; G <= 4; ++G)
         {
-            best_util = util;
-            best_R = R;
+            const int epe = (32 * G) / bgp;
+            if (epe < 1 || (size_t)epe * row_block * sizeof(double) > 40 * 1024)
+                continue; // one j0 row block of every hosted element must fit a staging buffer
+            const double util = (double)s.NB * epe / (double)(R * 32 * G);
+            const bool tie = util >= best_util - 1e-9 && util <= best_util + 1e-9;
+            const bool better = util > best_util + 1e-9 || (tie && (G < best_G || (G == best_G && M >= 9)));
+            if (better)
+            {
+                best_util = util;
+                best_R = R;
+                best_G = G;
+            }
         }
     }
     if (best_R == 0)
         return IB200_ERROR_UNSUPPORTED;
     const int R = plan.R = best_R;
     s.BGp = (s.NB + R - 1) / R;
-    s.G = s.BGp <= 32 ? 1 : (s.BGp + 31) / 32;
-    s.EPE = s.G == 1 ? 32 / s.BGp : 1;
+    s.G = best_G;
+    s.EPE = (32 * s.G) / s.BGp;
     // panels: about 6 KB of staged output per engine and buffer (all EPE elements together), at least one j0
-    const int row_block = n_out1 * s.N_in;
     s.PJ = std::max(1, std::min(n_out0, (int)(6144 / (sizeof(double) * row_block * s.EPE))));
     s.n_panels = (n_out0 + s.PJ - 1) / s.PJ;
     s.panel_cap = ((s.PJ * row_block + 2) + 1) & ~1;
     const size_t panel_bytes = sizeof(double) * s.EPE * s.panel_cap;
-    s.nbuf = panel_bytes * 2 <= 48 * 1024 ? 2 : 1;
-    const size_t engine_bytes = sizeof(double) * s.EPE * s.Qp + s.nbuf * panel_bytes;
-    // engines per CTA: up to 256 threads and 96 KB of shared memory
+    // The kernel is latency-bound below ~16 resident warps (measured on the C3 blocks: 8 -> 16 warps per SM is
+    // +25..40 %), so the second staging buffer is only kept when shared memory still allows 16 warps with it.
+    const size_t fixed_bytes = sizeof(double) * s.EPE * s.Qp;
+    const double warps_with_2 = 220.0 * 1024 / (double)(fixed_bytes + 2 * panel_bytes) * s.G;
+    s.nbuf = (warps_with_2 >= 16.0) ? 2 : 1;
+    if (const char *env = std::getenv("IB200_MASS_NBUF"))
+        s.nbuf = std::atoi(env) == 1 ? 1 : (std::atoi(env) == 2 ? 2 : s.nbuf);
+    const size_t engine_bytes = fixed_bytes + s.nbuf * panel_bytes;
+    // engines per CTA: up to 256 threads and ~100 KB of shared memory (two CTAs per SM)
     int epc = std::max(1, 256 / (32 * s.G));
-    while (epc > 1 && (epc * engine_bytes + sizeof(double) * 8 * M > 96 * 1024 || epc > 15))
+    while (epc > 1 && (epc * engine_bytes + sizeof(double) * 8 * M > 100 * 1024 || epc > 15))
         --epc;
     if (epc * engine_bytes + sizeof(double) * 8 * M > 200 * 1024)
         return IB200_ERROR_UNSUPPORTED;
