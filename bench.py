@@ -37,10 +37,10 @@ from interplib_b200 import synthetic as syn  # noqa: E402
 # bench line scales it to the elements of its own launch.  Slightly below the algorithmic bytes where the tail of the
 # output is still dirty in the 126 MB L2 when the kernel ends.
 NCU_TRAFFIC_BYTES = {
-    "c2": (1969330088, 1 << 20),   # profiles/r01_c2_eval2d_full.txt
+    "c2": (1970035944, 1 << 20),   # profiles/r01d_c2_eval2d_full.txt
     "c5": (5249943208, 1 << 20),   # profiles/r01c_c5_mass2d_lo_full.txt
     "c4": (5415202552, 1 << 13),   # profiles/r01_c4_mass2d_mma_full.txt
-    "c3": (1301776088, 1 << 15),   # profiles/r01_c3_mass2d_full.txt
+    "c3": (1415508904, 1 << 15),   # profiles/r01d_c3_mass2d_full.txt
     "c1": None,
 }
 

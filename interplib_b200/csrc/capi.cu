@@ -230,6 +230,8 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
     for (int i = 0; i < 8; ++i)
         for (int j = 0; j < 2; ++j)
             IB_CUDA(cudaEventCreate(&ctx->timer[i][j]));
+    IB_CUDA(cudaMalloc((void **)&ctx->sched_ring, sizeof(unsigned long long) * 2 * ib200_ctx::kSchedRing));
+    IB_CUDA(cudaMemset(ctx->sched_ring, 0, sizeof(unsigned long long) * 2 * ib200_ctx::kSchedRing));
     *out = ctx;
     return INTERP_SUCCESS;
 }
@@ -275,6 +277,7 @@ extern "C" int ib200_ctx_destroy(ib200_ctx_t *ctx)
     }
     cudaFree(ctx->scratch);
     cudaFree(ctx->dot_partial);
+    cudaFree(ctx->sched_ring);
     for (int i = 0; i < 8; ++i)
         for (int j = 0; j < 2; ++j)
             cudaEventDestroy(ctx->timer[i][j]);
@@ -638,7 +641,7 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
     const int n_arr = (int)arrays.size();
     if (where == IB200_DEVICE)
     {
-        LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+        LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
         // scratch arrays come from the context; bound them by running sub-chunks
         size_t scratch_per_elem = 0;
         for (auto &a : arrays)
@@ -764,7 +767,7 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
             }
             IB_CUDA(cudaMemcpyAsync(dev[i], src, cnt * a.elem_bytes, cudaMemcpyHostToDevice, st));
         }
-        LaunchCfg cfg{st, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+        LaunchCfg cfg{st, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
         IB_TRY(launch(cfg, first, cnt, dev.data()));
         for (int i = 0; i < n_arr; ++i)
         {
@@ -1160,7 +1163,7 @@ extern "C" int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const doub
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "a/b/out must not be NULL");
     if (where != IB200_DEVICE && where != IB200_HOST)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
-    LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches};
+    LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
     if (!ctx->dot_partial)
         IB_CUDA(cudaMalloc((void **)&ctx->dot_partial, sizeof(double) * (dot_scratch_doubles() + 1)));
     double *partial = ctx->dot_partial;

@@ -108,6 +108,13 @@ struct ib200_ctx
     void *scratch = nullptr;
     size_t scratch_bytes = 0;
     double *dot_partial = nullptr; // partial sums + result slot of ib200_dot
+    // dynamic tile scheduling: ring of {next tile, finished CTAs} counter pairs, zero between launches (the last CTA
+    // of a launch resets its pair); every LaunchCfg takes the next pair so launches in flight on different streams
+    // never share one
+    unsigned long long *sched_ring = nullptr;
+    unsigned sched_next = 0;
+    static constexpr unsigned kSchedRing = 256;
+    unsigned long long *next_sched() { return sched_ring + 2 * (sched_next++ % kSchedRing); }
 };
 
 int ctx_get_table(ib200_ctx *ctx, basis_spec_t b, integration_spec_t r, const DeviceTable **out);
@@ -125,6 +132,7 @@ struct LaunchCfg
     int sm_count;
     bool force_generic;
     unsigned long long *launch_counter;
+    unsigned long long *sched; // device counter pair {next tile, finished CTAs} for dynamically scheduled kernels
 };
 
 int launch_reconstruct_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *dofs, unsigned n_fields,
@@ -153,3 +161,28 @@ int launch_mass2d_lo(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &ke
                      const double *wsrc, double *out, const double *fvals = nullptr, double *rhs = nullptr);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);
+
+// ---- dynamic tile scheduling (device side) ----------------------------------------------------------------------
+// sched[0] = next unclaimed work item, sched[1] = participants that have finished.  SMs (and, for warp-autonomous
+// kernels, SM sub-partitions hosting different numbers of warps) do not drain an HBM-bound stream at the same rate;
+// with a static round-robin the fast ones idle at the end of the launch.
+#ifdef __CUDACC__
+// Closes a dynamically scheduled launch: the last participant (CTA or warp, `total` of them) to get here zeroes the
+// pair for the next launch.  Every participant has made its last claim before it arrives, so nobody reads sched[0]
+// after the reset.  Call from ONE thread per participant.
+__device__ __forceinline__ void sched_finish_one(unsigned long long *sched, unsigned long long total)
+{
+    __threadfence();
+    if (atomicAdd(sched + 1, 1ull) == total - 1)
+    {
+        sched[0] = 0;
+        sched[1] = 0;
+        __threadfence();
+    }
+}
+__device__ __forceinline__ void sched_finish(unsigned long long *sched)
+{
+    if (threadIdx.x == 0)
+        sched_finish_one(sched, gridDim.x);
+}
+#endif

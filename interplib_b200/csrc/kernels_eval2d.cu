@@ -72,7 +72,8 @@ constexpr int kWarps = 8;
 template <int N, int M, bool GRAD>
 __global__ void __launch_bounds__(kWarps * 32)
     eval2d_kernel(const __grid_constant__ Dim0Tabs<N, M> tab0, const double *__restrict__ B1g,
-                  const double *__restrict__ D1g, size_t E, const double *__restrict__ dofs, double *__restrict__ out)
+                  const double *__restrict__ D1g, size_t E, const double *__restrict__ dofs, double *__restrict__ out,
+                  unsigned long long *__restrict__ sched)
 {
     constexpr int EPW = 32 / M;         // elements per warp
     constexpr int EPB = EPW * kWarps;   // elements per tile
@@ -112,24 +113,41 @@ __global__ void __launch_bounds__(kWarps * 32)
     auto tile_elems = [&](size_t t) -> int { return (int)((t + 1) * EPB <= E ? EPB : E - t * EPB); };
     auto tile_is_bulk = [&](size_t t) -> bool { return base_aligned && ((tile_elems(t) * NN * sizeof(double)) % 16 == 0); };
 
+    // Dynamic tile scheduling: the first tile of a CTA is its block index, every further one is claimed from the
+    // global counter sched[0] (SMs do not drain an HBM-bound stream at the same rate; with a static round-robin the
+    // fast ones idle at the end).  Thread 0 keeps the claim two tiles ahead so the atomic's latency hides behind a
+    // whole tile of work, and hands tile indices to the CTA through next_tile[].
+    __shared__ size_t next_tile[2];
     unsigned phase[2] = {0, 0};
     size_t t = blockIdx.x;
-    if (t < n_tiles && tile_is_bulk(t) && threadIdx.x == 0)
+    size_t t_next = n_tiles, t_next2 = n_tiles; // meaningful in thread 0 only
+    if (threadIdx.x == 0)
     {
-        const unsigned bytes = tile_elems(t) * NN * sizeof(double);
-        mbar_expect_tx(&bar[0], bytes);
-        bulk_g2s(tile[0], dofs + t * (size_t)EPB * NN, bytes, &bar[0]);
+        if (t < n_tiles && tile_is_bulk(t))
+        {
+            const unsigned bytes = tile_elems(t) * NN * sizeof(double);
+            mbar_expect_tx(&bar[0], bytes);
+            bulk_g2s(tile[0], dofs + t * (size_t)EPB * NN, bytes, &bar[0]);
+        }
+        t_next = gridDim.x + atomicAdd(sched, 1ull);
+        t_next2 = gridDim.x + atomicAdd(sched, 1ull);
     }
-    for (int it = 0; t < n_tiles; ++it, t += gridDim.x)
+    for (int it = 0; t < n_tiles; ++it)
     {
         const int cur = it & 1;
-        const size_t t_next = t + gridDim.x;
         // buffer cur^1 was released by the __syncthreads() closing the previous iteration
-        if (t_next < n_tiles && tile_is_bulk(t_next) && threadIdx.x == 0)
+        if (threadIdx.x == 0)
         {
-            const unsigned bytes = tile_elems(t_next) * NN * sizeof(double);
-            mbar_expect_tx(&bar[cur ^ 1], bytes);
-            bulk_g2s(tile[cur ^ 1], dofs + t_next * (size_t)EPB * NN, bytes, &bar[cur ^ 1]);
+            if (t_next < n_tiles && tile_is_bulk(t_next))
+            {
+                const unsigned bytes = tile_elems(t_next) * NN * sizeof(double);
+                mbar_expect_tx(&bar[cur ^ 1], bytes);
+                bulk_g2s(tile[cur ^ 1], dofs + t_next * (size_t)EPB * NN, bytes, &bar[cur ^ 1]);
+            }
+            next_tile[cur ^ 1] = t_next;
+            t_next = t_next2;
+            if (t_next2 < n_tiles)
+                t_next2 = gridDim.x + atomicAdd(sched, 1ull);
         }
         const int n_here = tile_elems(t);
         if (tile_is_bulk(t))
@@ -189,7 +207,9 @@ __global__ void __launch_bounds__(kWarps * 32)
             }
         }
         __syncthreads();
+        t = next_tile[cur ^ 1];
     }
+    sched_finish(sched);
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -220,7 +240,8 @@ __device__ __forceinline__ double bilinear_term(const double t0[2], const double
 template <int N, int M>
 __global__ void __launch_bounds__(kWarps * 32)
     l2dual2d_kernel(const __grid_constant__ Dim0W<N, M> tab0, const double *__restrict__ Bw1g, const double *__restrict__ gtab,
-                    int wsrc, size_t E, const double *__restrict__ fvals, const double *__restrict__ aux, double *__restrict__ out)
+                    int wsrc, size_t E, const double *__restrict__ fvals, const double *__restrict__ aux, double *__restrict__ out,
+                    unsigned long long *__restrict__ sched)
 {
     constexpr int EPW = 32 / N;
     constexpr int EPB = EPW * kWarps;
@@ -273,16 +294,30 @@ __global__ void __launch_bounds__(kWarps * 32)
             bulk_g2s(atile[b], aux + t * (size_t)EPB * aux_per, ab, &bar[b]);
     };
 
+    // dynamic tile scheduling, as in eval2d_kernel
+    __shared__ size_t next_tile[2];
     unsigned phase[2] = {0, 0};
     size_t t = blockIdx.x;
-    if (t < n_tiles && tile_is_bulk(t) && threadIdx.x == 0)
-        issue(t, 0);
-    for (int it = 0; t < n_tiles; ++it, t += gridDim.x)
+    size_t t_next = n_tiles, t_next2 = n_tiles; // meaningful in thread 0 only
+    if (threadIdx.x == 0)
+    {
+        if (t < n_tiles && tile_is_bulk(t))
+            issue(t, 0);
+        t_next = gridDim.x + atomicAdd(sched, 1ull);
+        t_next2 = gridDim.x + atomicAdd(sched, 1ull);
+    }
+    for (int it = 0; t < n_tiles; ++it)
     {
         const int cur = it & 1;
-        const size_t t_next = t + gridDim.x;
-        if (t_next < n_tiles && tile_is_bulk(t_next) && threadIdx.x == 0)
-            issue(t_next, cur ^ 1);
+        if (threadIdx.x == 0)
+        {
+            if (t_next < n_tiles && tile_is_bulk(t_next))
+                issue(t_next, cur ^ 1);
+            next_tile[cur ^ 1] = t_next;
+            t_next = t_next2;
+            if (t_next2 < n_tiles)
+                t_next2 = gridDim.x + atomicAdd(sched, 1ull);
+        }
         const int n_here = tile_elems(t);
         if (tile_is_bulk(t))
         {
@@ -360,7 +395,9 @@ __global__ void __launch_bounds__(kWarps * 32)
             }
         }
         __syncthreads();
+        t = next_tile[cur ^ 1];
     }
+    sched_finish(sched);
 }
 
 template <int N, int M>
@@ -384,7 +421,7 @@ int launch_l2_one(const LaunchCfg &cfg, const double *d_tabs, const OpHost &host
         return IB200_ERROR_UNSUPPORTED;
     const size_t cap = (size_t)cfg.sm_count * per_sm;
     const int grid = (int)std::max<size_t>(1, n_tiles < cap ? n_tiles : cap);
-    l2dual2d_kernel<N, M><<<grid, kWarps * 32, smem_bytes, cfg.stream>>>(tab0, d_tabs, d_tabs + N * M, wsrc, E, fvals, aux, out);
+    l2dual2d_kernel<N, M><<<grid, kWarps * 32, smem_bytes, cfg.stream>>>(tab0, d_tabs, d_tabs + N * M, wsrc, E, fvals, aux, out, cfg.sched);
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)
@@ -417,7 +454,7 @@ int launch_one(const LaunchCfg &cfg, const OpDesc &op, const OpHost &host, size_
         per_sm = 1;
     const size_t cap = (size_t)cfg.sm_count * per_sm;
     const int grid = (int)(n_tiles < cap ? n_tiles : cap);
-    eval2d_kernel<N, M, GRAD><<<grid, kWarps * 32, 0, cfg.stream>>>(tab0, op.dim[1].Bin, op.dim[1].Din, E, dofs, out);
+    eval2d_kernel<N, M, GRAD><<<grid, kWarps * 32, 0, cfg.stream>>>(tab0, op.dim[1].Bin, op.dim[1].Din, E, dofs, out, cfg.sched);
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)

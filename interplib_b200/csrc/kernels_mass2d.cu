@@ -121,7 +121,8 @@ constexpr int min_blocks_for(int M, int R, bool /*symb*/)
 template <int M, int R, bool SYMB, int CAP>
 __global__ void __launch_bounds__(256, min_blocks_for(M, R, SYMB))
     mass2d_kernel(const __grid_constant__ MassParams<CAP> prm, const double *__restrict__ P1g, const int2 *__restrict__ bmap,
-                  const double *__restrict__ gtab, size_t E, const double *__restrict__ wsrc, double *__restrict__ out)
+                  const double *__restrict__ gtab, size_t E, const double *__restrict__ wsrc, double *__restrict__ out,
+                  unsigned long long *__restrict__ sched)
 {
     extern __shared__ __align__(16) double smem[];
     const MassShape &s = prm.s;
@@ -165,13 +166,33 @@ __global__ void __launch_bounds__(256, min_blocks_for(M, R, SYMB))
     const int bar_id = 1 + engine;
     unsigned panel_counter = 0;
 
-    for (size_t tile = (size_t)blockIdx.x * s.engines_per_cta + engine; tile < n_tiles; tile += n_engines)
+    // Dynamic scheduling per engine: the first tile is the engine's global index, every further one is claimed from
+    // sched[0] by the engine's first thread one tile ahead and handed over through eng_tile[engine][parity] across the
+    // barrier that opens a tile (written at the end of tile `it` into slot (it+1)&1, read after the next barrier).
+    __shared__ size_t eng_tile[8][2];
+    unsigned long long pend = 0;
+    if (t == 0)
     {
+        eng_tile[engine][0] = (size_t)blockIdx.x * s.engines_per_cta + engine;
+        pend = atomicAdd(sched, 1ull);
+    }
+    for (int it = 0;; ++it)
+    {
+        engine_barrier(bar_id, engine_threads); // stage-1 readers of the previous tile are done, eng_tile is visible
+        const size_t tile = eng_tile[engine][it & 1];
+        if (tile >= n_tiles)
+            break;
+        if (t == 0)
+        {
+            const size_t nt = n_engines + pend;
+            eng_tile[engine][(it + 1) & 1] = nt;
+            if (nt < n_tiles)
+                pend = atomicAdd(sched, 1ull);
+        }
         const size_t e = tile * s.EPE + el;
         const bool el_valid = lane_active && e < E;
 
         // ---- per-point weights of the tile's elements -> shared memory
-        engine_barrier(bar_id, engine_threads); // stage-1 readers of the previous tile are done
         if (el_valid)
         {
             double *W = Wsm + el * s.Qp;
@@ -339,6 +360,8 @@ __global__ void __launch_bounds__(256, min_blocks_for(M, R, SYMB))
     }
     if (issuer)
         bulk_wait_all();
+    if (t == 0)
+        sched_finish_one(sched, n_engines);
 }
 
 constexpr int cap_for(int M)
@@ -391,7 +414,7 @@ int launch_mass(const LaunchCfg &cfg, const MassPlan &plan, size_t E, const doub
     const size_t want = (n_tiles + shape.engines_per_cta - 1) / shape.engines_per_cta;
     const size_t cap = (size_t)cfg.sm_count * per_sm;
     const int grid = (int)std::max<size_t>(1, std::min(want, cap));
-    kernel<<<grid, threads, smem_bytes, cfg.stream>>>(prm, plan.d_P1, plan.d_bmap, plan.d_gtab, E, wsrc, out);
+    kernel<<<grid, threads, smem_bytes, cfg.stream>>>(prm, plan.d_P1, plan.d_bmap, plan.d_gtab, E, wsrc, out, cfg.sched);
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)

@@ -61,6 +61,10 @@ __device__ __forceinline__ void lo_fence_async_smem()
 // warp tile is one contiguous run of global memory).  Used for odd N, where the row panels of an element start and end
 // in the middle of 32-byte sectors: bulk stores of 2 000 B with sector-unaligned ends reach 5.58 TB/s, 20 000 B ones
 // 6.37 TB/s, aligned 2 KB ones 6.29 TB/s (tools/write_peak.cu, profiles/r01_write_peak.json).
+#ifndef IB200_LO_SCHED_CHUNK
+#define IB200_LO_SCHED_CHUNK 2
+#endif
+
 template <int N, int M, int R, bool TILE>
 struct LoShape
 {
@@ -101,7 +105,7 @@ template <int N, int M, int R, bool TILE>
 __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
     mass2d_lo_kernel(const __grid_constant__ LoParams<N, M> prm, const double *__restrict__ P1g, const int2 *__restrict__ offs, size_t E,
                      const double *__restrict__ wsrc, double *__restrict__ out, const double *__restrict__ fvals,
-                     double *__restrict__ rhs)
+                     double *__restrict__ rhs, unsigned long long *__restrict__ sched)
 {
     using S = LoShape<N, M, R, TILE>;
     extern __shared__ __align__(16) double smem[];
@@ -174,10 +178,28 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
                 pre_f[k] = (lane + 32 * k < nv * S::Q) ? fsrc[lane + 32 * k] : 0.0;
         }
     };
-    prefetch((size_t)blockIdx.x * S::WARPS + warp);
+    // Dynamic scheduling per warp, in chunks of CH consecutive tiles: the first chunk is the warp's global index, every
+    // further one is claimed from sched[0] by lane 0 one chunk ahead (the atomic's latency hides behind a whole chunk).
+    // Warps are autonomous and the FP64 pipe is per SM sub-partition: with 9 warps per SM a static split leaves the
+    // sub-partitions hosting two warps idle while the one hosting three finishes (16 % of the SMSP cycles, ncu).
+    constexpr size_t CH = IB200_LO_SCHED_CHUNK;
+    size_t tile = ((size_t)blockIdx.x * S::WARPS + warp) * CH, tile_end = tile + CH;
+    unsigned long long pend = 0;
+    if (lane == 0)
+        pend = atomicAdd(sched, 1ull);
+    prefetch(tile);
 
-    for (size_t tile = (size_t)blockIdx.x * S::WARPS + warp; tile < n_tiles; tile += n_warps)
+    while (tile < n_tiles)
     {
+        size_t tile_next = tile + 1, tile_next_end = tile_end;
+        if (tile_next >= tile_end)
+        {
+            const unsigned long long c = __shfl_sync(0xffffffffu, pend, 0);
+            tile_next = (n_warps + c) * CH;
+            tile_next_end = tile_next + CH;
+            if (lane == 0 && tile_next < n_tiles)
+                pend = atomicAdd(sched, 1ull);
+        }
         const size_t e = tile * S::EPW + el;
         const bool el_valid = lane_active && e < E;
 
@@ -195,7 +217,7 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
                     Insm[S::EPW * prm.aux_per + lane + 32 * k] = pre_f[k];
         }
         __syncwarp();
-        prefetch(tile + n_warps);
+        prefetch(tile_next);
         if (el_valid)
         {
             double *W = Wsm + el * S::Qp;
@@ -403,9 +425,13 @@ __global__ void __launch_bounds__(LoShape<N, M, R, TILE>::WARPS * 32)
             }
         }
         pc += S::NPANELS;
+        tile = tile_next;
+        tile_end = tile_next_end;
     }
     if (issuer)
         lo_bulk_wait_all();
+    if (lane == 0)
+        sched_finish_one(sched, n_warps);
 }
 
 struct LoPlan
@@ -577,10 +603,10 @@ int launch_lo(const LaunchCfg &cfg, LoPlan &plan, const OpHost &host, int wsrc_k
     if (per_sm < 1)
         return IB200_ERROR_UNSUPPORTED;
     const size_t n_tiles = (E + S::EPW - 1) / S::EPW;
-    const size_t want = (n_tiles + S::WARPS - 1) / S::WARPS;
+    const size_t want = (n_tiles + S::WARPS * IB200_LO_SCHED_CHUNK - 1) / (S::WARPS * IB200_LO_SCHED_CHUNK);
     const size_t cap = (size_t)cfg.sm_count * per_sm;
     const int grid = (int)std::max<size_t>(1, std::min(want, cap));
-    kernel<<<grid, S::WARPS * 32, smem_bytes, cfg.stream>>>(prm, plan.d_P1, plan.d_offs, E, wsrc, out, fvals, rhs);
+    kernel<<<grid, S::WARPS * 32, smem_bytes, cfg.stream>>>(prm, plan.d_P1, plan.d_offs, E, wsrc, out, fvals, rhs, cfg.sched);
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)
