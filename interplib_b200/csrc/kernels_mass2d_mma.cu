@@ -513,14 +513,70 @@ int build_mma_plan(const OpDesc &op, const OpHost &host, bool match0, bool match
         for (int i0 = 0; i0 < n_in0; ++i0)
             for (int q = 0; q < M; ++q)
                 P0[(size_t)(j0 * n_in0 + i0) * LDA + q] = host.w[0][q] * (host.Bout[0][j0 * M + q] * Tin0[i0 * M + q]);
-    std::vector<int2> boff;
+    // Column items b = (j1,i1) (pairs i1 <= j1 when the dimension-1 spaces match).  Their ORDER is free: eight consecutive
+    // items form one DMMA column tile, lane (quad_row, quad_col) stores columns 2*quad_col + v of its row, and a 64-bit
+    // shared-memory store is served per half warp (quad_row 0..3 x quad_col 0..3).  Rows of a tile sit 17 (= 1 mod 16)
+    // doubles apart, so the staging stores of a half warp are conflict-free iff the four items at columns {v, 2+v, 4+v,
+    // 6+v} have offsets that are pairwise >= 4 apart modulo 16 -- for the entry and for its mirror.  Greedy tile
+    // construction on that cost (row-major order had ~2-way conflicts on both stores, 41 % of all wavefronts, ncu).
+    struct Item
+    {
+        int j1, i1, od, om;
+    };
+    std::vector<Item> pool, items;
     for (int j1 = 0; j1 < n_out1; ++j1)
         for (int i1 = 0; i1 < (symb ? j1 + 1 : n_in1); ++i1)
+            pool.push_back({j1, i1, j1 * s.N_in + i1, (symb && i1 != j1) ? i1 * s.N_in + j1 : -1});
+    {
+        const int row_step = n_in1 % 16; // bank-slot step between consecutive rows a = (j0,i0) of a tile
+        auto store_cost = [&](const std::vector<Item> &tile, const Item &cand, bool mirror) {
+            // extra wavefronts when `cand` takes the next column of `tile`: lanes of the same parity v collide when
+            // (offset + quad_row*row_step) mod 16 coincide
+            const int c = (int)tile.size(), v = c & 1;
+            const int oc = mirror ? cand.om : cand.od;
+            if (oc < 0)
+                return 0;
+            int cost = 0;
+            for (int k = v; k < c; k += 2)
+            {
+                const int ok = mirror ? tile[k].om : tile[k].od;
+                if (ok < 0)
+                    continue;
+                for (int ra = 0; ra < 4; ++ra)
+                    for (int rb = 0; rb < 4; ++rb)
+                        if (((oc + ra * row_step) - (ok + rb * row_step)) % 16 == 0)
+                            ++cost;
+            }
+            return cost;
+        };
+        std::vector<Item> tile;
+        while (!pool.empty())
         {
-            boff.push_back(make_int2(j1 * s.N_in + i1, (symb && i1 != j1) ? i1 * s.N_in + j1 : -1));
-            for (int q = 0; q < LDA; ++q)
-                P1.push_back(q < M ? host.w[1][q] * (host.Bout[1][j1 * M + q] * Tin1[i1 * M + q]) : 0.0);
+            size_t best_i = 0;
+            int best_c = 1 << 30;
+            for (size_t i = 0; i < pool.size(); ++i)
+            {
+                const int c = store_cost(tile, pool[i], false) + store_cost(tile, pool[i], true);
+                if (c < best_c)
+                {
+                    best_c = c;
+                    best_i = i;
+                }
+            }
+            tile.push_back(pool[best_i]);
+            items.push_back(pool[best_i]);
+            pool.erase(pool.begin() + (long)best_i);
+            if (tile.size() == 8)
+                tile.clear();
         }
+    }
+    std::vector<int2> boff;
+    for (const Item &it : items)
+    {
+        boff.push_back(make_int2(it.od, it.om));
+        for (int q = 0; q < LDA; ++q)
+            P1.push_back(q < M ? host.w[1][q] * (host.Bout[1][it.j1 * M + q] * Tin1[it.i1 * M + q]) : 0.0);
+    }
     s.NB = (int)boff.size();
     s.CT = (s.NB + 7) / 8;
     boff.resize((size_t)s.CT * 8, make_int2(-1, -1));
