@@ -198,6 +198,20 @@ IB200_API int ib200_reconstruct_batch(ib200_ctx_t *ctx, unsigned ndim, const bas
                                       const integration_spec_t *rules, size_t n_elements, const double *dofs,
                                       unsigned n_fields, const unsigned *deriv_masks, double *out, int where);
 
+/* ---- N2: arbitrary reference points, element batched --------------------------- */
+/* FunctionSpace.evaluate (src/python/function_space_objects.c:142-276 ->
+ * basis_compute_outer_product_basis, src/basis/basis_set.c:577-633) for n_points points per
+ * element: x[E][ndim][P] -> out[E][P][N], out = ((1 * b0[i0]) * b1[i1]) * ...  (1..3 dimensions). */
+IB200_API int ib200_evaluate_points_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, size_t n_elements,
+                                          size_t n_points, const double *x, double *out, int where);
+/* reconstruct(dof, *x), python/interplib/degrees_of_freedom.py:10-37, with optional reference
+ * derivatives (BasisSpecs.derivatives, src/basis/basis_set.c:491-556, per flagged dimension):
+ *   out[e][f][p] = sum_i dofs[e][i] * prod_k T_k[i_k](x[e][k][p]),  T_k = basis derivative if bit k
+ * of deriv_masks[f] is set.  dofs[E][N], x[E][ndim][P], out[E][n_fields][P]. */
+IB200_API int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, size_t n_elements,
+                                             const double *dofs, size_t n_points, const double *x, unsigned n_fields,
+                                             const unsigned *deriv_masks, double *out, int where);
+
 /* ---- A9 (K0): batched element geometry ---------------------------------------------------- */
 /* coordinate_map_new + space_map_new, src/python/mappings.c:8-90, 304-556 with
  * matrix_qr_decompose / matrix_back_substitute (src/operations/matrices.c:15-86, 117-141).

@@ -171,6 +171,39 @@ class Context:
                                           len(deriv_masks), masks, _ptr(out), where))
         return out
 
+    # -- N2 ----------------------------------------------------------------------------------------
+    def evaluate_points(self, basis, x, out=None, where=HOST, n_elements=None, n_points=None):
+        """x[E][ndim][P] -> out[E][P][N]: FunctionSpace.evaluate per element   (ib200_evaluate_points_batch)"""
+        N, ndim = _n_basis(basis), len(basis)
+        if where == HOST:
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            assert x.ndim == 3 and x.shape[1] == ndim, "x must be [E][ndim][P]"
+            E, P = x.shape[0], x.shape[2]
+            if out is None:
+                out = np.empty((E, P, N))
+        else:
+            E, P = int(n_elements), int(n_points)
+        check(lib.ib200_evaluate_points_batch(self.handle, ndim, basis_specs(basis), E, P, _ptr(x), _ptr(out), where))
+        return out
+
+    def reconstruct_points(self, basis, dofs, x, deriv_masks=(0,), out=None, where=HOST, n_elements=None, n_points=None):
+        """dofs[E][N], x[E][ndim][P] -> out[E][n_fields][P]: reconstruct() per element   (ib200_reconstruct_points_batch)"""
+        N, ndim = _n_basis(basis), len(basis)
+        masks = (C.c_uint * len(deriv_masks))(*[int(m) for m in deriv_masks])
+        if where == HOST:
+            dofs = _as_in(dofs, (-1, N))
+            E = dofs.shape[0]
+            x = np.ascontiguousarray(x, dtype=np.float64)
+            assert x.ndim == 3 and x.shape[0] == E and x.shape[1] == ndim, "x must be [E][ndim][P]"
+            P = x.shape[2]
+            if out is None:
+                out = np.empty((E, len(deriv_masks), P))
+        else:
+            E, P = int(n_elements), int(n_points)
+        check(lib.ib200_reconstruct_points_batch(self.handle, ndim, basis_specs(basis), E, _ptr(dofs), P, _ptr(x),
+                                                 len(deriv_masks), masks, _ptr(out), where))
+        return out
+
     # -- K0 ----------------------------------------------------------------------------------------
     def geometry(self, geom_basis, rules, geom_dofs, n_phys, want=("coords", "det", "jinv"), where=HOST, n_elements=None,
                  coords=None, det=None, jinv=None):

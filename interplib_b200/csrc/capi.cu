@@ -255,6 +255,9 @@ extern "C" int ib200_ctx_clear_cache(ib200_ctx_t *ctx)
         cudaFree(kv.second.d_values);
     for (auto &kv : ctx->rules)
         cudaFree(kv.second.d_nodes);
+    for (auto &kv : ctx->point_tabs)
+        cudaFree(kv.second);
+    ctx->point_tabs.clear();
     ctx->tables.clear();
     ctx->rules.clear();
     ctx->plans.clear();
@@ -848,6 +851,89 @@ extern "C" int ib200_reconstruct_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
                            return launch_reconstruct_generic(cfg, op, cnt, (const double *)dev[0], n_fields, masks,
                                                              (double *)dev[1]);
                        });
+}
+
+// ---- N2: arbitrary reference points -------------------------------------------------------------------------
+static int ctx_make_point_op(ib200_ctx *ctx, unsigned ndim, const basis_spec_t *basis, PointOp *op)
+{
+    if (ndim == 0 || ndim > IB200_POINT_MAX_DIM || !basis)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "arbitrary-point evaluation takes 1..%d dimensions (got %u)",
+                          IB200_POINT_MAX_DIM, ndim);
+    op->ndim = (int)ndim;
+    op->N = 1;
+    for (unsigned k = 0; k < ndim; ++k)
+    {
+        PointDim &d = op->dim[k];
+        d.type = (int)basis[k].type;
+        d.n = (int)basis[k].order + 1;
+        d.roots = d.den = nullptr;
+        op->N *= d.n;
+        if (ib200_tables_is_lagrange(basis[k].type))
+        {
+            const auto key = std::make_tuple((int)basis[k].type, basis[k].order);
+            auto it = ctx->point_tabs.find(key);
+            if (it == ctx->point_tabs.end())
+            {
+                std::vector<double> h(2 * (size_t)d.n);
+                IB_TRY(ib200_tables_lagrange_roots_denominators(basis[k], h.data(), h.data() + d.n));
+                double *dev = nullptr;
+                IB_CUDA(cudaMalloc((void **)&dev, sizeof(double) * h.size()));
+                IB_CUDA(cudaMemcpy(dev, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice));
+                it = ctx->point_tabs.emplace(key, dev).first;
+            }
+            d.roots = it->second;
+            d.den = it->second + d.n;
+        }
+        else if (basis[k].type != BASIS_LEGENDRE && basis[k].type != BASIS_BERNSTEIN)
+            return ib200_fail(INTERP_ERROR_INVALID_ENUM, "unknown basis type %d", (int)basis[k].type);
+    }
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_evaluate_points_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, size_t n_elements,
+                                           size_t n_points, const double *x, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (n_elements && n_points && (!x || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "x/out must not be NULL");
+    PointOp op;
+    IB_TRY(ctx_make_point_op(ctx, ndim, basis, &op));
+    if (n_points == 0)
+        return INTERP_SUCCESS;
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)x, sizeof(double) * ndim * n_points},
+                                      {ARR_OUT, out, sizeof(double) * n_points * op.N}};
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        return launch_points_evaluate(cfg, op, cnt, n_points, (const double *)dev[0], (double *)dev[1]);
+    });
+}
+
+extern "C" int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, size_t n_elements,
+                                              const double *dofs, size_t n_points, const double *x, unsigned n_fields,
+                                              const unsigned *deriv_masks, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (!deriv_masks || n_fields == 0 || n_fields > 8)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..8 fields and their derivative masks");
+    if (n_elements && n_points && (!dofs || !x || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "dofs/x/out must not be NULL");
+    for (unsigned f = 0; f < n_fields; ++f)
+        if (deriv_masks[f] >> ndim)
+            return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "derivative mask 0x%x names a dimension >= %u", deriv_masks[f], ndim);
+    PointOp op;
+    IB_TRY(ctx_make_point_op(ctx, ndim, basis, &op));
+    if (n_points == 0)
+        return INTERP_SUCCESS;
+    unsigned masks[8];
+    std::copy(deriv_masks, deriv_masks + n_fields, masks);
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)dofs, sizeof(double) * op.N},
+                                      {ARR_IN, (void *)x, sizeof(double) * ndim * n_points},
+                                      {ARR_OUT, out, sizeof(double) * n_fields * n_points}};
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        return launch_points_reconstruct(cfg, op, cnt, n_points, (const double *)dev[0], (const double *)dev[1], n_fields, masks,
+                                         (double *)dev[2]);
+    });
 }
 
 // ---- K0 ----------------------------------------------------------------------------------------------------

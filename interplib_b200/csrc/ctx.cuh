@@ -68,6 +68,23 @@ struct OpHost
     const double *w[IB200_MAX_DIM];
 };
 
+// Arbitrary-point evaluation (kernels_points.cu): per dimension the basis family, its size and, for the Lagrange family,
+// device pointers to the nodes and to the denominators prod_{k != j} (r_j - r_k).
+#define IB200_POINT_MAX_DIM 3
+struct PointDim
+{
+    int type; // basis_set_type_t
+    int n;
+    const double *roots;
+    const double *den;
+};
+struct PointOp
+{
+    int ndim;
+    PointDim dim[IB200_POINT_MAX_DIM];
+    int N;
+};
+
 // ---- host-side context ----------------------------------------------------------------------------
 struct DeviceTable
 {
@@ -95,6 +112,7 @@ struct ib200_ctx
     std::map<std::tuple<int, unsigned, int, unsigned>, DeviceTable> tables;
     std::map<std::tuple<int, unsigned>, DeviceRule> rules;
     std::map<std::string, std::shared_ptr<void>> plans; // per-operation kernel plans (kernels_mass2d.cu)
+    std::map<std::tuple<int, unsigned>, double *> point_tabs; // Lagrange roots[n] | denominators[n] per (type, order)
     unsigned long long launches = 0;
     bool force_generic = false;
     int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
@@ -143,6 +161,9 @@ int launch_mass_generic(const LaunchCfg &cfg, const OpDesc &op, bool symmetric, 
                         int deriv_dim_in, double *out);
 int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *fvals, const double *det, double *out);
 int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs);
+int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out);
+int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
+                              unsigned n_fields, const unsigned *masks, double *out);
 int dot_scratch_doubles();
 int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b, double *partial, double *out);
 

@@ -1,0 +1,242 @@
+// N2 -- tensor-product basis evaluation and reconstruction at ARBITRARY reference points, element batched.
+//
+//   evaluate:     out[e][p][i]   = ((1 * b0_{i0}(x0)) * b1_{i1}(x1)) * ...          i = (i0,i1,..) row-major
+//   reconstruct:  out[e][f][p]   = sum_i dofs[e][i] * prod_k T^k_f,{i_k}(x_k[e][p]),    T^k_f = d/dxi_k basis if bit k of
+//                                                                                      masks[f] is set, else the basis
+//
+// replaces FunctionSpace.evaluate (/root/reference/src/python/function_space_objects.c:142-276 ->
+// basis_compute_outer_product_basis, src/basis/basis_set.c:577-633, 1-D evaluators :462-556) and
+// reconstruct() (/root/reference/python/interplib/degrees_of_freedom.py:10-37) which the reference runs once per
+// element on the host.  Points are given per element and dimension: x[e][k][p].
+//
+// One thread per (element, point): the 1-D values (and derivatives) of every dimension are formed in registers / local
+// memory in the operation order of the reference's evaluators (Bonnet recursion, degree-raising Bernstein recursion,
+// Lagrange numerator product in ascending node order divided by the host-built denominator), the contraction with the
+// element's DoFs is sum-factorised per point, DoFs are read through the read-only path (the threads of a block share
+// an element).  Not a roofline-tuned kernel: it is the caller-side companion of K1 (sampling geometry, plotting).
+#include <algorithm>
+
+#include "ctx.cuh"
+
+namespace
+{
+
+constexpr int PT_MAXN = 24; // 1-D basis functions per dimension (p <= 23)
+
+struct PointMasks
+{
+    unsigned m[8];
+};
+
+__device__ void pt_basis_1d(const PointDim &pd, double x, double *v, double *dv, bool want_d)
+{
+    const int n = pd.n;
+    if (pd.type == BASIS_LEGENDRE)
+    {
+        // legendre_eval_bonnet_all, src/polynomials/legendre.c:60-85; derivative recurrence of basis_set.c:494-513
+        v[0] = 1.0;
+        if (n > 1)
+            v[1] = x;
+        double lo = 1.0, hi = x;
+        for (int k = 2; k < n; ++k)
+        {
+            const double a = __dmul_rn((double)(2 * k - 1), x);
+            const double next = __ddiv_rn(__dsub_rn(__dmul_rn(a, hi), __dmul_rn((double)(k - 1), lo)), (double)k);
+            v[k] = next;
+            lo = hi;
+            hi = next;
+        }
+        if (want_d)
+        {
+            double d = 0.0;
+            dv[0] = 0.0;
+            for (int i = 1; i < n; ++i)
+            {
+                d = __dadd_rn(__dmul_rn((double)i, v[i - 1]), __dmul_rn(x, d));
+                dv[i] = d;
+            }
+        }
+        return;
+    }
+    if (pd.type == BASIS_BERNSTEIN)
+    {
+        // bernstein_interpolation_vector, src/polynomials/bernstein.c:31-51 at t = (x + 1) / 2
+        const double t = __dmul_rn(__dadd_rn(x, 1.0), 0.5);
+        const double a = __dsub_rn(1.0, t), b = t;
+        const int deg = n - 1;
+        if (want_d)
+        {
+            // degree deg-1 polynomials first (they give the derivative), then one more raising step for the values
+            if (deg == 0)
+            {
+                v[0] = 1.0;
+                dv[0] = 0.0;
+                return;
+            }
+            double w[PT_MAXN];
+            w[0] = 1.0;
+            for (int i = 0; i < deg - 1; ++i)
+            {
+                w[i + 1] = __dmul_rn(w[i], b);
+                for (int j = i; j > 0; --j)
+                    w[j] = __dadd_rn(__dmul_rn(b, w[j - 1]), __dmul_rn(a, w[j]));
+                w[0] = __dmul_rn(w[0], a);
+            }
+            v[deg] = __dmul_rn(w[deg - 1], b);
+            for (int j = deg - 1; j > 0; --j)
+                v[j] = __dadd_rn(__dmul_rn(b, w[j - 1]), __dmul_rn(a, w[j]));
+            v[0] = __dmul_rn(w[0], a);
+            dv[deg] = __dmul_rn((double)deg, w[deg - 1]);
+            for (int j = deg - 1; j > 0; --j)
+                dv[j] = __dmul_rn((double)deg, __dsub_rn(w[j - 1], w[j]));
+            dv[0] = __dmul_rn(w[0], -(double)deg);
+            for (int j = 0; j < n; ++j)
+                dv[j] = __dmul_rn(dv[j], 0.5);
+            return;
+        }
+        v[0] = 1.0;
+        for (int i = 0; i < deg; ++i)
+        {
+            v[i + 1] = __dmul_rn(v[i], b);
+            for (int j = i; j > 0; --j)
+                v[j] = __dadd_rn(__dmul_rn(b, v[j - 1]), __dmul_rn(a, v[j]));
+            v[0] = __dmul_rn(v[0], a);
+        }
+        return;
+    }
+    // Lagrange family: lagrange_polynomial_values_2 / _first_derivative_2, src/polynomials/lagrange.c:108-183, 383-525
+    double dif[PT_MAXN];
+    for (int j = 0; j < n; ++j)
+        dif[j] = __dsub_rn(x, pd.roots[j]);
+    for (int j = 0; j < n; ++j)
+    {
+        // value: product of the differences in ascending node order, divided by the denominator last;
+        // derivative: the same running product carried together with its x-derivative
+        double acc = 1.0, der = 0.0;
+        for (int k = 0; k < n; ++k)
+        {
+            if (k == j)
+                continue;
+            der = fma(der, dif[k], acc);
+            acc = __dmul_rn(acc, dif[k]);
+        }
+        v[j] = n == 1 ? 1.0 : __ddiv_rn(acc, pd.den[j]);
+        if (want_d)
+            dv[j] = n == 1 ? 0.0 : __ddiv_rn(der, pd.den[j]);
+    }
+}
+
+__global__ void __launch_bounds__(128)
+    points_evaluate_kernel(const PointOp op, size_t E, size_t P, const double *__restrict__ x, double *__restrict__ out)
+{
+    const size_t total = E * P;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = idx / P, p = idx - e * P;
+        double b[IB200_POINT_MAX_DIM][PT_MAXN];
+        for (int k = 0; k < op.ndim; ++k)
+            pt_basis_1d(op.dim[k], x[(e * op.ndim + k) * P + p], b[k], nullptr, false);
+        double *o = out + idx * (size_t)op.N;
+        const int n1 = op.ndim > 1 ? op.dim[1].n : 1, n2 = op.ndim > 2 ? op.dim[2].n : 1;
+        for (int i0 = 0; i0 < op.dim[0].n; ++i0)
+        {
+            const double v0 = __dmul_rn(1.0, b[0][i0]);
+            for (int i1 = 0; i1 < n1; ++i1)
+            {
+                const double v1 = op.ndim > 1 ? __dmul_rn(v0, b[1][i1]) : v0;
+                for (int i2 = 0; i2 < n2; ++i2)
+                    o[((size_t)i0 * n1 + i1) * n2 + i2] = op.ndim > 2 ? __dmul_rn(v1, b[2][i2]) : v1;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+    points_reconstruct_kernel(const PointOp op, size_t E, size_t P, const double *__restrict__ dofs, const double *__restrict__ x,
+                              int n_fields, const PointMasks masks, bool any_deriv, double *__restrict__ out)
+{
+    // a block walks the points of ONE element at a time (blockIdx.y strides over elements) so that the DoF reads of
+    // its threads are broadcasts
+    for (size_t e = blockIdx.y; e < E; e += gridDim.y)
+    {
+        const double *c = dofs + e * (size_t)op.N;
+        for (size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x; p < P; p += (size_t)gridDim.x * blockDim.x)
+        {
+            double b[IB200_POINT_MAX_DIM][PT_MAXN], d[IB200_POINT_MAX_DIM][PT_MAXN];
+            for (int k = 0; k < op.ndim; ++k)
+                pt_basis_1d(op.dim[k], x[(e * op.ndim + k) * P + p], b[k], d[k], any_deriv);
+            const int n0 = op.dim[0].n, n1 = op.ndim > 1 ? op.dim[1].n : 1, n2 = op.ndim > 2 ? op.dim[2].n : 1;
+            for (int f = 0; f < n_fields; ++f)
+            {
+                const unsigned m = masks.m[f];
+                const double *t0 = (m & 1u) ? d[0] : b[0];
+                const double *t1 = (m & 2u) ? d[1] : b[1];
+                const double *t2 = (m & 4u) ? d[2] : b[2];
+                double acc0 = 0.0;
+                for (int i0 = 0; i0 < n0; ++i0)
+                {
+                    double acc1 = 0.0;
+                    for (int i1 = 0; i1 < n1; ++i1)
+                    {
+                        const double *row = c + ((size_t)i0 * n1 + i1) * n2;
+                        double acc2 = 0.0;
+                        if (op.ndim > 2)
+                        {
+                            for (int i2 = 0; i2 < n2; ++i2)
+                                acc2 = fma(__ldg(row + i2), t2[i2], acc2);
+                        }
+                        else
+                            acc2 = __ldg(row);
+                        acc1 = op.ndim > 1 ? fma(acc2, t1[i1], acc1) : acc2;
+                    }
+                    acc0 = fma(acc1, t0[i0], acc0);
+                }
+                out[(e * n_fields + f) * P + p] = acc0;
+            }
+        }
+    }
+}
+
+} // namespace
+
+int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out)
+{
+    if (E == 0 || P == 0)
+        return INTERP_SUCCESS;
+    for (int k = 0; k < op.ndim; ++k)
+        if (op.dim[k].n > PT_MAXN)
+            return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
+    const size_t total = E * P;
+    const int grid = (int)std::min<size_t>((total + 127) / 128, (size_t)cfg.sm_count * 16);
+    points_evaluate_kernel<<<grid, 128, 0, cfg.stream>>>(op, E, P, x, out);
+    ++*cfg.launch_counter;
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "launch of points_evaluate_kernel failed: %s", cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}
+
+int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
+                              unsigned n_fields, const unsigned *masks, double *out)
+{
+    PointMasks pm{};
+    bool any_deriv = false;
+    for (unsigned f = 0; f < n_fields && f < 8; ++f)
+    {
+        pm.m[f] = masks[f];
+        any_deriv = any_deriv || masks[f] != 0;
+    }
+    if (E == 0 || P == 0 || n_fields == 0)
+        return INTERP_SUCCESS;
+    for (int k = 0; k < op.ndim; ++k)
+        if (op.dim[k].n > PT_MAXN)
+            return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
+    const unsigned gx = (unsigned)std::min<size_t>((P + 127) / 128, 1024);
+    const unsigned gy = (unsigned)std::min<size_t>(E, std::max<size_t>(1, (size_t)cfg.sm_count * 16 / gx));
+    points_reconstruct_kernel<<<dim3(gx, gy), 128, 0, cfg.stream>>>(op, E, P, dofs, x, (int)n_fields, pm, any_deriv, out);
+    ++*cfg.launch_counter;
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "launch of points_reconstruct_kernel failed: %s", cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}

@@ -226,6 +226,18 @@ static double lagrange_denominator(unsigned n, const double *r, unsigned j)
     return d;
 }
 
+/* roots[n] then denominators[n] of a Lagrange basis (device arbitrary-point evaluation, kernels_points.cu) */
+int ib200_tables_lagrange_roots_denominators(basis_spec_t spec, double *roots, double *den)
+{
+    const unsigned n = spec.order + 1;
+    const int res = ib200_tables_lagrange_roots(spec, roots);
+    if (res != INTERP_SUCCESS)
+        return res;
+    for (unsigned j = 0; j < n; ++j)
+        den[j] = lagrange_denominator(n, roots, j);
+    return INTERP_SUCCESS;
+}
+
 /* ((v / (r_j - r_0)) / (r_j - r_1)) ... : lagrange_polynomial_denominators_apply_stride,
  * src/polynomials/lagrange.c:261-274 */
 static double lagrange_divide_chain(unsigned n, const double *r, unsigned j, double v)

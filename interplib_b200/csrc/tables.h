@@ -11,6 +11,7 @@ int ib200_tables_rule(integration_spec_t spec, double *nodes, double *weights, u
 int ib200_tables_order_for_accuracy(integration_rule_type_t type, unsigned accuracy, unsigned *order);
 int ib200_tables_is_lagrange(basis_set_type_t type);
 int ib200_tables_lagrange_roots(basis_spec_t spec, double *roots);
+int ib200_tables_lagrange_roots_denominators(basis_spec_t spec, double *roots, double *den);
 int ib200_tables_basis(basis_spec_t basis, integration_spec_t rule, double *values, double *derivs);
 int ib200_tables_space_weights(unsigned ndim, const integration_spec_t *rules, double *weights);
 int ib200_tables_space_nodes(unsigned ndim, const integration_spec_t *rules, double *nodes);

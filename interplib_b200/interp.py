@@ -23,7 +23,7 @@ from ._lib import BASIS_TYPES, RULE_TYPES
 __all__ = [
     "BasisType", "IntegrationMethod", "IntegrationRegistry", "IntegrationSpecs", "IntegrationSpace", "BasisRegistry",
     "BasisSpecs", "FunctionSpace", "DegreesOfFreedom", "CoordinateMap", "SpaceMap", "compute_mass_matrix",
-    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct",
+    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct", "reconstruct_batch",
     "compute_dual_degrees_of_freedom", "DEFAULT_INTEGRATION_REGISTRY", "DEFAULT_BASIS_REGISTRY",
 ]
 
@@ -614,6 +614,31 @@ def reconstruct(dof: DegreesOfFreedom, *x) -> np.ndarray:
             raise ValueError("All input coordinate arrays must have the same shape.")
     phi = dof.function_space.evaluate(*xs).reshape((-1, dof.n_dofs))
     return np.sum(phi * dof.values.flatten(), axis=-1).reshape(xs[0].shape)
+
+
+def reconstruct_batch(function_space: FunctionSpace, dof_values, *x, idim: Sequence[int] = ()) -> np.ndarray:
+    """Element-batched :func:`reconstruct` on the GPU (ib200_reconstruct_points_batch):
+    ``dof_values[E, n0, n1, ..]`` and one coordinate array ``x_k[E, ...]`` per dimension (same shape, leading axis =
+    element) -> values ``[E, ...]``; ``idim`` lists reference dimensions to differentiate along (each once)."""
+    d = function_space.dimension
+    if len(x) != d:
+        raise TypeError(f"reconstruct_batch() takes {d} coordinate arrays, {len(x)} were given.")
+    xs = [np.ascontiguousarray(v, dtype=np.float64) for v in x]
+    for v in xs[1:]:
+        if v.shape != xs[0].shape:
+            raise ValueError("All input coordinate arrays must have the same shape.")
+    dof_values = np.ascontiguousarray(dof_values, dtype=np.float64)
+    E = dof_values.shape[0]
+    if xs[0].shape[:1] != (E,) or dof_values.size != E * function_space.n_basis:
+        raise ValueError("dof_values must be [E, n0, n1, ..] and every coordinate array [E, ...].")
+    mask = 0
+    for k in idim:
+        if not 0 <= int(k) < d or (mask >> int(k)) & 1:
+            raise ValueError(f"Invalid or repeated derivative dimension {k}.")
+        mask |= 1 << int(k)
+    pts = np.stack([v.reshape(E, -1) for v in xs], axis=1)  # [E][d][P]
+    out = _ctx().reconstruct_points(function_space.basis, dof_values.reshape(E, -1), pts, [mask])
+    return out[:, 0, :].reshape(xs[0].shape)
 
 
 def compute_dual_degrees_of_freedom(fn: Callable, integration_space: IntegrationSpace, function_space: FunctionSpace, /) -> DegreesOfFreedom:

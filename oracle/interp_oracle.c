@@ -24,6 +24,11 @@
  *                       compute_gradient_mass_matrix          src/python/mass_matrices.c:341-565
  *   orc_l2_dual         projection_l2_dual                    python/interplib/integration.py:106-168
  *   orc_space_weights   integration_space_weights             src/python/integration_objects.c:633-716
+ *   orc_evaluate_points FunctionSpace.evaluate                src/python/function_space_objects.c:142-276,
+ *                       basis_compute_outer_product_basis     src/basis/basis_set.c:462-633,
+ *                       lagrange_polynomial_values_2 / _first_derivative_2
+ *                                                              src/polynomials/lagrange.c:108-183, 383-525
+ *   orc_reconstruct_points  reconstruct                       python/interplib/degrees_of_freedom.py:10-37
  *
  * Parity status: PINNED -- validated `==` against the reference itself compiled in this
  * container (oracle/build_ref.py) and against the golden vectors in tests/golden/ that the same
@@ -416,6 +421,190 @@ static inline void unflatten(size_t flat, unsigned ndim, const unsigned *ext, un
         idx[k] = (unsigned)(flat % ext[k]);
         flat /= ext[k];
     }
+}
+
+/* ------------------------------------------------------------------ arbitrary points (N2) -- */
+
+/* basis_compute_at_point_values / _derivatives for ONE call of cnt points, /root/reference/src/basis/basis_set.c:462-556:
+ * out[p*n + j].  Lagrange: lagrange_polynomial_values_2 (src/polynomials/lagrange.c:108-183: the numerator product is
+ * divided by the denominator last, except at the final point of the call where the quotient comes first) and
+ * lagrange_polynomial_first_derivative_2 (:383-525: summed pair numerators over the denominator, the last two points
+ * divided by the root differences pair by pair). */
+static int point_basis(int btype, unsigned order, size_t cnt, const double *x, double *val, double *der)
+{
+    const unsigned n = order + 1;
+    if (btype == B_LEGENDRE || btype == B_BERNSTEIN)
+    {
+        /* the table builders evaluate point by point with exactly the evaluators of basis_set.c:462-556; they write
+         * basis-major [n][cnt], transpose into point-major */
+        double *B = malloc(sizeof(double) * 2 * n * (cnt ? cnt : 1));
+        double *D = B + n * (cnt ? cnt : 1);
+        if (btype == B_LEGENDRE)
+            legendre_tables(order, (unsigned)cnt, x, B, D);
+        else
+            bernstein_tables(order, (unsigned)cnt, x, B, D);
+        for (size_t p = 0; p < cnt; ++p)
+            for (unsigned j = 0; j < n; ++j)
+            {
+                if (val)
+                    val[p * n + j] = B[j * cnt + p];
+                if (der)
+                    der[p * n + j] = D[j * cnt + p];
+            }
+        free(B);
+        return 0;
+    }
+    double *r = malloc(sizeof(double) * 4 * n);
+    double *den = r + n, *dif = r + 2 * n, *col = r + 3 * n;
+    const int res = orc_roots(btype, order, r);
+    if (res)
+    {
+        free(r);
+        return res;
+    }
+    lag_denominators(n, r, den);
+    for (size_t p = 0; p < cnt; ++p)
+    {
+        if (val)
+        {
+            double *row = val + p * n;
+            if (n == 1)
+                row[0] = 1.0;
+            else
+            {
+                const int last = p + 1 == cnt;
+                const double d0 = x[p] - r[0];
+                row[0] = last ? 1.0 / den[0] : 1.0;
+                for (unsigned j = 1; j < n; ++j)
+                    row[j] = last ? +d0 / den[j] : +d0;
+                for (unsigned i = 1; i < n; ++i)
+                {
+                    const double di = x[p] - r[i];
+                    for (unsigned j = 0; j < n; ++j)
+                        if (j != i)
+                            row[j] *= +di;
+                }
+                if (!last)
+                    for (unsigned j = 0; j < n; ++j)
+                        row[j] /= den[j];
+            }
+        }
+        if (der)
+        {
+            for (unsigned j = 0; j < n; ++j)
+            {
+                dif[j] = x[p] - r[j];
+                col[j] = 0.0;
+            }
+            for (unsigned i = 0; i < n; ++i)
+                for (unsigned j = 0; j < i; ++j)
+                {
+                    double term = 1.0;
+                    for (unsigned l = 0; l < n; ++l)
+                        if (l != i && l != j)
+                            term *= dif[l];
+                    col[j] += term;
+                    col[i] += term;
+                }
+            if (p + 2 < cnt)
+                for (unsigned j = 0; j < n; ++j)
+                    col[j] /= den[j];
+            else
+                lag_divide_pairs(n, r, col);
+            for (unsigned j = 0; j < n; ++j)
+                der[p * n + j] = col[j];
+        }
+    }
+    free(r);
+    return 0;
+}
+
+/* FunctionSpace.evaluate per element (basis_compute_outer_product_basis, src/basis/basis_set.c:577-633):
+ * x[E][ndim][P] -> out[E][P][N], running product over the dimensions in ascending order starting from 1 */
+int orc_evaluate_points(unsigned ndim, const int *btype, const unsigned *border, size_t E, size_t P, const double *x,
+                        double *out)
+{
+    if (ndim == 0 || ndim > ORC_MAX_DIM)
+        return 102;
+    unsigned n[ORC_MAX_DIM];
+    size_t N = 1;
+    for (unsigned k = 0; k < ndim; ++k)
+        N *= (n[k] = border[k] + 1);
+    int fail = 0;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (size_t e = 0; e < E; ++e)
+    {
+        double *tab[ORC_MAX_DIM] = {0};
+        for (unsigned k = 0; k < ndim; ++k)
+        {
+            tab[k] = malloc(sizeof(double) * (P ? P : 1) * n[k]);
+            if (point_basis(btype[k], border[k], P, x + (e * ndim + k) * P, tab[k], NULL))
+                fail = 1;
+        }
+        for (size_t p = 0; p < P; ++p)
+            for (size_t i = 0; i < N; ++i)
+            {
+                unsigned idx[ORC_MAX_DIM];
+                unflatten(i, ndim, n, idx);
+                double v = 1.0;
+                for (unsigned k = 0; k < ndim; ++k)
+                    v = v * tab[k][p * n[k] + idx[k]];
+                out[(e * P + p) * N + i] = v;
+            }
+        for (unsigned k = 0; k < ndim; ++k)
+            free(tab[k]);
+    }
+    return fail ? 104 : 0;
+}
+
+/* reconstruct(dof, *x), python/interplib/degrees_of_freedom.py:10-37: sum_i evaluate(x)[p][i] * dofs[i]; with a
+ * derivative mask the flagged dimensions use BasisSpecs.derivatives (basis_compute_at_point_derivatives).  The sum over
+ * i runs in flat order (NumPy sums the contiguous last axis pairwise in blocks; the difference is O(eps)).
+ * dofs[E][N], x[E][ndim][P] -> out[E][n_fields][P] */
+int orc_reconstruct_points(unsigned ndim, const int *btype, const unsigned *border, size_t E, const double *dofs, size_t P,
+                           const double *x, unsigned n_fields, const unsigned *masks, double *out)
+{
+    if (ndim == 0 || ndim > ORC_MAX_DIM)
+        return 102;
+    unsigned n[ORC_MAX_DIM];
+    size_t N = 1;
+    for (unsigned k = 0; k < ndim; ++k)
+        N *= (n[k] = border[k] + 1);
+    int fail = 0;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (size_t e = 0; e < E; ++e)
+    {
+        double *val[ORC_MAX_DIM] = {0}, *der[ORC_MAX_DIM] = {0};
+        for (unsigned k = 0; k < ndim; ++k)
+        {
+            val[k] = malloc(sizeof(double) * 2 * (P ? P : 1) * n[k]);
+            der[k] = val[k] + (P ? P : 1) * n[k];
+            if (point_basis(btype[k], border[k], P, x + (e * ndim + k) * P, val[k], der[k]))
+                fail = 1;
+        }
+        for (unsigned f = 0; f < n_fields; ++f)
+            for (size_t p = 0; p < P; ++p)
+            {
+                double acc = 0.0;
+                for (size_t i = 0; i < N; ++i)
+                {
+                    unsigned idx[ORC_MAX_DIM];
+                    unflatten(i, ndim, n, idx);
+                    double v = 1.0;
+                    for (unsigned k = 0; k < ndim; ++k)
+                        v = v * (((masks[f] >> k) & 1u) ? der[k] : val[k])[p * n[k] + idx[k]];
+                    acc += v * dofs[e * N + i];
+                }
+                out[(e * n_fields + f) * P + p] = acc;
+            }
+        for (unsigned k = 0; k < ndim; ++k)
+            free(val[k]);
+    }
+    return fail ? 104 : 0;
 }
 
 int orc_space_weights(unsigned ndim, const int *rtype, const unsigned *rorder, double *W)

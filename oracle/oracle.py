@@ -127,6 +127,33 @@ def reconstruct(basis, rules, dofs, deriv_masks=(0,)):
     return out
 
 
+def evaluate_points(basis, x):
+    """x[E][ndim][P] -> out[E][P][N]   (FunctionSpace.evaluate per element)"""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    E, ndim, P = x.shape
+    N = int(np.prod([o + 1 for _, o in basis]))
+    out = np.empty((E, P, N))
+    bt, bo = _split(basis, BASIS_TYPES)
+    _chk(lib().orc_evaluate_points(C.c_uint(ndim), bt, bo, C.c_size_t(E), C.c_size_t(P), _dp(x), _dp(out)), "evaluate_points")
+    return out
+
+
+def reconstruct_points(basis, dofs, x, deriv_masks=(0,)):
+    """dofs[E][N], x[E][ndim][P] -> out[E][n_fields][P]   (reconstruct() per element)"""
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    E, ndim, P = x.shape
+    N = int(np.prod([o + 1 for _, o in basis]))
+    dofs = np.ascontiguousarray(dofs, dtype=np.float64).reshape(E, N)
+    out = np.empty((E, len(deriv_masks), P))
+    bt, bo = _split(basis, BASIS_TYPES)
+    _chk(
+        lib().orc_reconstruct_points(C.c_uint(ndim), bt, bo, C.c_size_t(E), _dp(dofs), C.c_size_t(P), _dp(x),
+                                     C.c_uint(len(deriv_masks)), _uints(deriv_masks), _dp(out)),
+        "reconstruct_points",
+    )
+    return out
+
+
 def geometry(geom_basis, rules, geom_dofs, n_phys, want_coords=True, want_det=True, want_jinv=True):
     """geom_dofs[E][n_phys][Ng] -> coords[E][n_phys][1+d][Q], det[E][Q], jinv[E][Q][d][n_phys]"""
     Ng, Q = _counts(geom_basis, rules)

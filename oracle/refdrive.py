@@ -151,3 +151,39 @@ def l2_dual(basis, rules, fvals, geom_basis=None, geom_dofs=None, n_phys=0):
         dual = ip.projection_l2_dual(lambda *x, fe=fe: fe, fs, integ)
         out[e] = np.asarray(dual.values).reshape(-1)
     return out
+
+
+def evaluate_points(basis, x):
+    """FunctionSpace.evaluate per element: x[E][ndim][P] -> [E][P][N]"""
+    ip = ref()
+    fs = _fs(ip, basis)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    E, ndim, P = x.shape
+    N = int(np.prod([o + 1 for _, o in basis]))
+    out = np.empty((E, P, N))
+    for e in range(E):
+        out[e] = np.asarray(fs.evaluate(*(np.ascontiguousarray(x[e, k]) for k in range(ndim)))).reshape(P, N)
+    return out
+
+
+def reconstruct_points(basis, dofs, x):
+    """interplib.reconstruct(dof, *x) per element: dofs[E][N], x[E][ndim][P] -> [E][P]"""
+    ip = ref()
+    fs = _fs(ip, basis)
+    shape = [o + 1 for _, o in basis]
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    E, ndim, P = x.shape
+    dofs = np.asarray(dofs, dtype=np.float64).reshape(E, -1)
+    out = np.empty((E, P))
+    for e in range(E):
+        dof = ip.DegreesOfFreedom(fs, dofs[e].reshape(shape))
+        out[e] = ip.reconstruct(dof, *(np.ascontiguousarray(x[e, k]) for k in range(ndim)))
+    return out
+
+
+def basis_points_1d(basis1, x):
+    """BasisSpecs.values / .derivatives at the points x[P] -> ([P][n], [P][n])"""
+    ip = ref()
+    b = ip.BasisSpecs(*basis1)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    return np.asarray(b.values(x)).reshape(len(x), -1), np.asarray(b.derivatives(x)).reshape(len(x), -1)

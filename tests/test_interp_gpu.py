@@ -222,3 +222,23 @@ def test_gradient_mass_matrix_on_a_line_and_an_affine_quad():
     for j in range(2):
         total = sum(compute_gradient_mass_matrix(fs2, fs2_out, smap2, i, j) @ u2 for i in range(2))
         assert total == approx(projection_l2_dual(grads[j], fs2_out, smap2).values.flatten(), rel=1e-9)
+
+
+def test_reconstruct_batch_matches_per_element_reconstruct():
+    """tests/test_dofs.py:74-100 in batched form: reconstruct_batch (GPU, N2) == reconstruct() of every element."""
+    from interplib_b200.interp import DegreesOfFreedom, reconstruct, reconstruct_batch
+
+    fs = _space([("lagrange-gauss-lobatto", 4), ("bernstein", 3)])
+    rng = np.random.default_rng(21)
+    E = 17
+    vals = rng.random((E, 5, 4))
+    x, y = rng.uniform(-1, 1, (E, 6, 3)), rng.uniform(-1, 1, (E, 6, 3))
+    got = reconstruct_batch(fs, vals, x, y)
+    assert got.shape == (E, 6, 3)
+    for e in range(E):
+        ref = reconstruct(DegreesOfFreedom(fs, vals[e]), x[e], y[e])
+        assert got[e] == approx(ref, rel=1e-12, abs=1e-13)
+    with pytest.raises(ValueError):
+        reconstruct_batch(fs, vals, x, y, idim=[0, 0])
+    with pytest.raises(TypeError):
+        reconstruct_batch(fs, vals, x)
