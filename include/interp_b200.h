@@ -212,6 +212,16 @@ IB200_API int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, co
                                              const double *dofs, size_t n_points, const double *x, unsigned n_fields,
                                              const unsigned *deriv_masks, double *out, int where);
 
+/* ---- N3: incidence matrix and derivative DoFs ---------------------------------- */
+/* incidence_matrix(basis_specs), src/python/incidence.c:38-110: out[n][n+1], n = basis.order >= 1
+ * (host; Bernstein / Legendre integer patterns, Lagrange by lagrange_polynomial_first_derivative_2). */
+IB200_API int ib200_incidence_matrix(basis_spec_t basis, double *out);
+/* DegreesOfFreedom.derivative(idim), src/python/degrees_of_freedom.c:738-945, for a batch of elements:
+ * dofs[E][n_0+1]..[n_idim+1]..  ->  out[E][n_0+1]..[n_idim]..  (the space one order lower along idim);
+ * additions in the reference's order, bit-identical results. */
+IB200_API int ib200_dof_derivative_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, unsigned idim,
+                                         size_t n_elements, const double *dofs, double *out, int where);
+
 /* ---- A9 (K0): batched element geometry ---------------------------------------------------- */
 /* coordinate_map_new + space_map_new, src/python/mappings.c:8-90, 304-556 with
  * matrix_qr_decompose / matrix_back_substitute (src/operations/matrices.c:15-86, 117-141).

@@ -106,6 +106,11 @@ _PROTOTYPES = {
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint,
          C.POINTER(C.c_uint), C.c_void_p, C.c_int],
     ),
+    "ib200_incidence_matrix": (C.c_int, [BasisSpec, C.c_void_p]),
+    "ib200_dof_derivative_batch": (
+        C.c_int,
+        [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int],
+    ),
     "ib200_geometry_batch": (
         C.c_int,
         [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_size_t, C.c_void_p,

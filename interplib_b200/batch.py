@@ -204,6 +204,22 @@ class Context:
                                                  len(deriv_masks), masks, _ptr(out), where))
         return out
 
+    # -- N3 ----------------------------------------------------------------------------------------
+    def dof_derivative(self, basis, dofs, idim, out=None, where=HOST, n_elements=None):
+        """dofs[E][N] -> DoFs of d/dxi_idim in the space one order lower along idim   (ib200_dof_derivative_batch)"""
+        N = _n_basis(basis)
+        lower = [(t, o - 1 if k == idim else o) for k, (t, o) in enumerate(basis)]
+        if where == HOST:
+            dofs = _as_in(dofs, (-1, N))
+            E = dofs.shape[0]
+            if out is None:
+                out = np.empty((E, _n_basis(lower) if 0 <= idim < len(basis) and basis[idim][1] > 0 else 0))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_dof_derivative_batch(self.handle, len(basis), basis_specs(basis), int(idim), E, _ptr(dofs), _ptr(out),
+                                             where))
+        return out
+
     # -- K0 ----------------------------------------------------------------------------------------
     def geometry(self, geom_basis, rules, geom_dofs, n_phys, want=("coords", "det", "jinv"), where=HOST, n_elements=None,
                  coords=None, det=None, jinv=None):
@@ -376,6 +392,14 @@ def basis_table_1d(basis, rule):
     check(lib.ib200_basis_table_1d(basis_specs([basis])[0], rule_specs([rule])[0], B.ctypes.data_as(_lib._dp),
                                    D.ctypes.data_as(_lib._dp)))
     return B, D
+
+
+def incidence_matrix(basis):
+    """[n][n+1] derivative-DoF operator of a 1-D basis (ib200_incidence_matrix; src/python/incidence.c:38-110)."""
+    bt, bo = basis
+    out = np.empty((max(bo, 0), bo + 1))
+    check(lib.ib200_incidence_matrix(basis_specs([basis])[0], out.ctypes.data_as(C.c_void_p)))
+    return out
 
 
 def integration_space_weights(rules):

@@ -258,6 +258,9 @@ extern "C" int ib200_ctx_clear_cache(ib200_ctx_t *ctx)
     for (auto &kv : ctx->point_tabs)
         cudaFree(kv.second);
     ctx->point_tabs.clear();
+    for (auto &kv : ctx->inc_tabs)
+        cudaFree(kv.second);
+    ctx->inc_tabs.clear();
     ctx->tables.clear();
     ctx->rules.clear();
     ctx->plans.clear();
@@ -933,6 +936,65 @@ extern "C" int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, c
     return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
         return launch_points_reconstruct(cfg, op, cnt, n_points, (const double *)dev[0], (const double *)dev[1], n_fields, masks,
                                          (double *)dev[2]);
+    });
+}
+
+// ---- N3: incidence / derivative DoFs ------------------------------------------------------------------------
+extern "C" int ib200_incidence_matrix(basis_spec_t basis, double *out)
+{
+    if (!out)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "out must not be NULL");
+    if (basis.order == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Cannot compute the incidence matrix for a zero-dimensional basis.");
+    const int res = ib200_tables_incidence_matrix(basis, out);
+    if (res != INTERP_SUCCESS)
+        return ib200_fail(res, "incidence matrix: unknown basis type %d", (int)basis.type);
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_dof_derivative_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, unsigned idim,
+                                          size_t n_elements, const double *dofs, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    if (ndim == 0 || ndim > IB200_MAX_DIM || !basis)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..%d dimensions", (int)IB200_MAX_DIM);
+    if (idim >= ndim)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Expected an index between 0 and %u, but got %u.", ndim - 1, idim);
+    if (basis[idim].order == 0)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT,
+                          "Cannot compute the derivative of a function with order 0 in dimension %u.", idim);
+    if (n_elements && (!dofs || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "dofs/out must not be NULL");
+    size_t pre = 1, post = 1;
+    for (unsigned k = 0; k < idim; ++k)
+        pre *= basis[k].order + 1;
+    for (unsigned k = idim + 1; k < ndim; ++k)
+        post *= basis[k].order + 1;
+    const int n = (int)basis[idim].order;
+    const double *d_inc = nullptr;
+    if (ib200_tables_is_lagrange(basis[idim].type))
+    {
+        const auto key = std::make_tuple((int)basis[idim].type, basis[idim].order);
+        auto it = ctx->inc_tabs.find(key);
+        if (it == ctx->inc_tabs.end())
+        {
+            std::vector<double> h((size_t)n * (n + 1));
+            IB_TRY(ib200_tables_incidence_matrix(basis[idim], h.data()));
+            double *dev = nullptr;
+            IB_CUDA(cudaMalloc((void **)&dev, sizeof(double) * h.size()));
+            IB_CUDA(cudaMemcpy(dev, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice));
+            it = ctx->inc_tabs.emplace(key, dev).first;
+        }
+        d_inc = it->second;
+    }
+    else if (basis[idim].type != BASIS_LEGENDRE && basis[idim].type != BASIS_BERNSTEIN)
+        return ib200_fail(INTERP_ERROR_INVALID_ENUM, "Unsupported basis type %d.", (int)basis[idim].type);
+    const int type = (int)basis[idim].type;
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)dofs, sizeof(double) * pre * (n + 1) * post},
+                                      {ARR_OUT, out, sizeof(double) * pre * n * post}};
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        return launch_dof_derivative(cfg, type, n, pre, post, d_inc, cnt, (const double *)dev[0], (double *)dev[1]);
     });
 }
 

@@ -113,6 +113,7 @@ struct ib200_ctx
     std::map<std::tuple<int, unsigned>, DeviceRule> rules;
     std::map<std::string, std::shared_ptr<void>> plans; // per-operation kernel plans (kernels_mass2d.cu)
     std::map<std::tuple<int, unsigned>, double *> point_tabs; // Lagrange roots[n] | denominators[n] per (type, order)
+    std::map<std::tuple<int, unsigned>, double *> inc_tabs;   // Lagrange incidence matrices [n][n+1] per (type, order)
     unsigned long long launches = 0;
     bool force_generic = false;
     int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
@@ -164,6 +165,8 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
 int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out);
 int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
                               unsigned n_fields, const unsigned *masks, double *out);
+int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, size_t post, const double *d_inc, size_t E,
+                          const double *in, double *out);
 int dot_scratch_doubles();
 int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b, double *partial, double *out);
 

@@ -197,7 +197,64 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+// N3 -- DegreesOfFreedom.derivative(idim), /root/reference/src/python/degrees_of_freedom.c:738-945: the 1-D incidence
+// operator [n][n+1] (src/python/incidence.c:38-110) applied along one dimension of every element's DoF tensor,
+//   out[e][pre][row][post] = sum_col Inc[row][col] * in[e][pre][col][post].
+// One thread per output value; the additions run in the reference's order with separate roundings (Bernstein: (0 - c*in[r])
+// + c*in[r+1]; Legendre: columns r+1, r+3, .. descending, weight 2r+1; Lagrange: columns ascending from 0), so the
+// result is bit-identical to the reference's.
+__global__ void __launch_bounds__(256)
+    dof_derivative_kernel(int type, int n, size_t pre, size_t post, const double *__restrict__ inc, size_t E,
+                          const double *__restrict__ in, double *__restrict__ out)
+{
+    const size_t per_out = pre * (size_t)n * post, per_in = pre * (size_t)(n + 1) * post;
+    const size_t total = E * per_out;
+    for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = idx / per_out, rem = idx - e * per_out;
+        const size_t i_pre = rem / ((size_t)n * post), r2 = rem - i_pre * (size_t)n * post;
+        const int row = (int)(r2 / post);
+        const size_t i_post = r2 - (size_t)row * post;
+        const double *src = in + e * per_in + i_pre * (size_t)(n + 1) * post + i_post;
+        double v = 0.0;
+        if (type == BASIS_BERNSTEIN)
+        {
+            const double c = (double)n / 2.0;
+            v = __dadd_rn(__dsub_rn(0.0, __dmul_rn(c, src[(size_t)row * post])), __dmul_rn(c, src[(size_t)(row + 1) * post]));
+        }
+        else if (type == BASIS_LEGENDRE)
+        {
+            const double w = (double)(2 * row + 1);
+            int col = row + 1 + 2 * ((n - row - 1) / 2); // largest column <= n with the parity of row + 1
+            for (; col > row; col -= 2)
+                v = __dadd_rn(v, __dmul_rn(w, src[(size_t)col * post]));
+        }
+        else
+        {
+            const double *m = inc + (size_t)row * (n + 1);
+            for (int col = 0; col <= n; ++col)
+                v = __dadd_rn(v, __dmul_rn(m[col], src[(size_t)col * post]));
+        }
+        out[idx] = v;
+    }
+}
+
 } // namespace
+
+int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, size_t post, const double *d_inc, size_t E,
+                          const double *in, double *out)
+{
+    const size_t total = E * pre * (size_t)n * post;
+    if (total == 0)
+        return INTERP_SUCCESS;
+    const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)cfg.sm_count * 8);
+    dof_derivative_kernel<<<grid, 256, 0, cfg.stream>>>(type, n, pre, post, d_inc, E, in, out);
+    ++*cfg.launch_counter;
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "launch of dof_derivative_kernel failed: %s", cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}
 
 int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out)
 {

@@ -693,3 +693,57 @@ int ib200_tables_function_space_evaluate(unsigned ndim, const basis_spec_t *basi
         free(tab[k]);
     return res;
 }
+
+/* N3 -- incidence_matrix(basis_specs), /root/reference/src/python/incidence.c:38-110: the [n][n+1] matrix (n = order)
+ * that maps the DoFs of a 1-D function to the DoFs of its derivative in the space one order lower.  Bernstein and
+ * Legendre: closed-form integer patterns; Lagrange: l_col'(node_row of the order n-1 basis) by
+ * lagrange_polynomial_first_derivative_2 (the last two rows divide pair by pair, as in basis_at_points above). */
+int ib200_tables_incidence_matrix(basis_spec_t basis, double *out)
+{
+    const unsigned n = basis.order;
+    if (n == 0)
+        return IB200_ERROR_BAD_ARGUMENT;
+    memset(out, 0, sizeof(double) * n * (n + 1));
+    switch (basis.type)
+    {
+    case BASIS_BERNSTEIN: {
+        const double coeff = (double)n / 2.0;
+        out[0] = -coeff;
+        for (unsigned col = 1; col < n; ++col)
+        {
+            out[col * (n + 1) + col] = -coeff;
+            out[(col - 1) * (n + 1) + col] = +coeff;
+        }
+        out[(n - 1) * (n + 1) + n] = +coeff;
+        return INTERP_SUCCESS;
+    }
+    case BASIS_LEGENDRE:
+        /* d/dx P_col = sum over r = col-1, col-3, .. of (2r+1) P_r */
+        for (unsigned col = 1; col <= n; ++col)
+            for (unsigned r = col - 1;; r -= 2)
+            {
+                out[r * (n + 1) + col] = (double)(2 * r + 1);
+                if (r < 2)
+                    break;
+            }
+        return INTERP_SUCCESS;
+    case BASIS_LAGRANGE_GAUSS:
+    case BASIS_LAGRANGE_UNIFORM:
+    case BASIS_LAGRANGE_GAUSS_LOBATTO:
+    case BASIS_LAGRANGE_CHEBYSHEV_GAUSS: {
+        double *nodes = malloc(sizeof(double) * n);
+        if (!nodes)
+            return INTERP_ERROR_FAILED_ALLOCATION;
+        basis_spec_t lower = basis;
+        lower.order = n - 1;
+        int res = ib200_tables_lagrange_roots(lower, nodes);
+        if (res == INTERP_SUCCESS)
+            res = ib200_tables_basis_at_points(basis, n, nodes, NULL, out);
+        free(nodes);
+        return res;
+    }
+    default:
+        return INTERP_ERROR_INVALID_ENUM;
+    }
+}
+

@@ -21,6 +21,8 @@ int ib200_tables_basis_at_points(basis_spec_t basis, size_t cnt, const double *x
 int ib200_tables_function_space_evaluate(unsigned ndim, const basis_spec_t *basis, size_t cnt,
                                          const double *const *x, double *out);
 
+int ib200_tables_incidence_matrix(basis_spec_t basis, double *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,7 +23,7 @@ from ._lib import BASIS_TYPES, RULE_TYPES
 __all__ = [
     "BasisType", "IntegrationMethod", "IntegrationRegistry", "IntegrationSpecs", "IntegrationSpace", "BasisRegistry",
     "BasisSpecs", "FunctionSpace", "DegreesOfFreedom", "CoordinateMap", "SpaceMap", "compute_mass_matrix",
-    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct", "reconstruct_batch",
+    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct", "reconstruct_batch", "incidence_matrix",
     "compute_dual_degrees_of_freedom", "DEFAULT_INTEGRATION_REGISTRY", "DEFAULT_BASIS_REGISTRY",
 ]
 
@@ -411,6 +411,30 @@ class DegreesOfFreedom:
                 raise ValueError(f"Expected each index to appear only once, but got it twice at index {idx}.")
             mask |= 1 << int(idx)
         return self._reconstruct(integration_space, mask, integration_registry, basis_registry, out)
+
+    def derivative(self, idim: int, /) -> "DegreesOfFreedom":
+        """DoFs of the derivative along reference dimension ``idim`` in the space one order lower along it
+        (degrees_of_freedom.c:853-945; ib200_dof_derivative_batch with a batch of one, bit-identical)."""
+        ndim = self._fs.dimension
+        if not isinstance(idim, (int, np.integer)):
+            raise TypeError(f"Expected an integer index, got {type(idim).__name__}.")
+        if idim < 0 or idim >= ndim:
+            raise ValueError(f"Expected an index between 0 and {ndim - 1}, but got {idim}.")
+        if self._fs.basis[idim][1] == 0:
+            raise ValueError(f"Cannot compute the derivative of a function with order 0 in dimension {idim}.")
+        lower = self._fs.lower_order(int(idim))
+        vals = _ctx().dof_derivative(self._fs.basis, self._values.reshape(1, -1), int(idim))
+        return DegreesOfFreedom(lower, vals.reshape(lower.shape))
+
+
+def incidence_matrix(basis_specs: "BasisSpecs", /) -> np.ndarray:
+    """``[n, n+1]`` matrix taking the DoFs of a 1-D function to those of its derivative, one order lower
+    (src/python/incidence.c:6-110; host table layer, bit-identical)."""
+    if not isinstance(basis_specs, BasisSpecs):
+        raise TypeError(f"Expected BasisSpecs, got {type(basis_specs).__name__}")
+    if basis_specs.order == 0:
+        raise ValueError("Cannot compute the incidence matrix for a zero-dimensional basis.")
+    return batch.incidence_matrix(basis_specs.spec)
 
 
 # ------------------------------------------------------------------------------------------------ geometry

@@ -29,6 +29,8 @@
  *                       lagrange_polynomial_values_2 / _first_derivative_2
  *                                                              src/polynomials/lagrange.c:108-183, 383-525
  *   orc_reconstruct_points  reconstruct                       python/interplib/degrees_of_freedom.py:10-37
+ *   orc_incidence_matrix    incidence_matrix                  src/python/incidence.c:38-110
+ *   orc_dof_derivative      DegreesOfFreedom.derivative       src/python/degrees_of_freedom.c:738-945
  *
  * Parity status: PINNED -- validated `==` against the reference itself compiled in this
  * container (oracle/build_ref.py) and against the golden vectors in tests/golden/ that the same
@@ -605,6 +607,122 @@ int orc_reconstruct_points(unsigned ndim, const int *btype, const unsigned *bord
             free(val[k]);
     }
     return fail ? 104 : 0;
+}
+
+/* ------------------------------------------------------------------ incidence (N3) -------- */
+
+/* incidence_matrix, /root/reference/src/python/incidence.c:38-110: out[n][n+1], n = order >= 1 */
+int orc_incidence_matrix(int btype, unsigned order, double *out)
+{
+    const unsigned n = order;
+    if (n == 0)
+        return 102;
+    memset(out, 0, sizeof(double) * n * (n + 1));
+    if (btype == B_BERNSTEIN)
+    {
+        const double coeff = (double)n / 2.0;
+        out[0 * (n + 1) + 0] = -coeff;
+        for (unsigned col = 1; col < n; ++col)
+        {
+            out[col * (n + 1) + col] = -coeff;
+            out[(col - 1) * (n + 1) + col] = +coeff;
+        }
+        out[(n - 1) * (n + 1) + n] = +coeff;
+        return 0;
+    }
+    if (btype == B_LEGENDRE)
+    {
+        for (unsigned col = n; col > 0; --col)
+        {
+            unsigned coeff = 2 * col - 1;
+            for (unsigned c_row = 0; 2 * c_row < col; ++c_row)
+            {
+                const unsigned r = (col - 1 - 2 * c_row);
+                out[r * (n + 1) + col] = coeff;
+                coeff -= 4;
+            }
+        }
+        return 0;
+    }
+    /* Lagrange: first derivative of the order-n basis at the nodes of the order n-1 basis */
+    double *nodes = malloc(sizeof(double) * n);
+    int res = orc_roots(btype, n - 1, nodes);
+    if (res == 0)
+        res = point_basis(btype, n, n, nodes, NULL, out);
+    free(nodes);
+    return res;
+}
+
+/* DegreesOfFreedom.derivative(idim), src/python/degrees_of_freedom.c:738-945 (the three apply routines :738-851),
+ * per element: in[E][pre][n+1][post] -> out[E][pre][n][post] */
+int orc_dof_derivative(unsigned ndim, const int *btype, const unsigned *border, unsigned idim, size_t E, const double *in,
+                       double *out)
+{
+    if (ndim == 0 || ndim > ORC_MAX_DIM || idim >= ndim || border[idim] == 0)
+        return 102;
+    size_t pre = 1, post = 1;
+    for (unsigned k = 0; k < idim; ++k)
+        pre *= border[k] + 1;
+    for (unsigned k = idim + 1; k < ndim; ++k)
+        post *= border[k] + 1;
+    const unsigned n = border[idim];
+    const int type = btype[idim];
+    double *mat = NULL;
+    if (type != B_BERNSTEIN && type != B_LEGENDRE)
+    {
+        mat = malloc(sizeof(double) * n * (n + 1));
+        const int res = orc_incidence_matrix(type, n, mat);
+        if (res)
+        {
+            free(mat);
+            return res;
+        }
+    }
+    memset(out, 0, sizeof(double) * E * pre * n * post); /* a fresh DegreesOfFreedom object holds zeros */
+    for (size_t e = 0; e < E; ++e)
+        for (size_t i_pre = 0; i_pre < pre; ++i_pre)
+            for (size_t i_post = 0; i_post < post; ++i_post)
+            {
+                double *po = out + e * pre * n * post + i_pre * n * post + i_post;
+                const double *pi = in + e * pre * (n + 1) * post + i_pre * (n + 1) * post + i_post;
+                if (type == B_BERNSTEIN)
+                {
+                    const double coeff = (double)n / 2.0;
+                    po[0] -= coeff * pi[0];
+                    for (unsigned col = 1; col < n; ++col)
+                    {
+                        const double x = coeff * pi[col * post];
+                        po[col * post] -= x;
+                        po[(col - 1) * post] += x;
+                    }
+                    po[(n - 1) * post] += coeff * pi[n * post];
+                }
+                else if (type == B_LEGENDRE)
+                {
+                    for (unsigned col = n; col > 0; --col)
+                    {
+                        unsigned coeff = 2 * col - 1;
+                        for (unsigned c_row = 0; 2 * c_row < col; ++c_row)
+                        {
+                            const unsigned r = (col - 1 - 2 * c_row);
+                            po[r * post] += coeff * pi[col * post];
+                            coeff -= 4;
+                        }
+                    }
+                }
+                else
+                {
+                    for (unsigned row = 0; row < n; ++row)
+                    {
+                        double v = 0;
+                        for (unsigned col = 0; col < n + 1; ++col)
+                            v += mat[row * (n + 1) + col] * pi[col * post];
+                        po[row * post] = v;
+                    }
+                }
+            }
+    free(mat);
+    return 0;
 }
 
 int orc_space_weights(unsigned ndim, const int *rtype, const unsigned *rorder, double *W)

@@ -154,6 +154,27 @@ def reconstruct_points(basis, dofs, x, deriv_masks=(0,)):
     return out
 
 
+def incidence_matrix(basis1):
+    """[n][n+1] (incidence_matrix of a 1-D basis)"""
+    (bt,), (bo,) = [BASIS_TYPES[basis1[0]]], [basis1[1]]
+    out = np.empty((bo, bo + 1))
+    _chk(lib().orc_incidence_matrix(C.c_int(bt), C.c_uint(bo), _dp(out)), "incidence_matrix")
+    return out
+
+
+def dof_derivative(basis, dofs, idim):
+    """dofs[E][N] -> [E][N_lower]   (DegreesOfFreedom.derivative per element)"""
+    N = int(np.prod([o + 1 for _, o in basis]))
+    Nl = int(np.prod([o + (0 if k == idim else 1) for k, (_, o) in enumerate(basis)]))
+    dofs = np.ascontiguousarray(dofs, dtype=np.float64).reshape(-1, N)
+    E = dofs.shape[0]
+    out = np.empty((E, Nl))
+    bt, bo = _split(basis, BASIS_TYPES)
+    _chk(lib().orc_dof_derivative(C.c_uint(len(basis)), bt, bo, C.c_uint(idim), C.c_size_t(E), _dp(dofs), _dp(out)),
+         "dof_derivative")
+    return out
+
+
 def geometry(geom_basis, rules, geom_dofs, n_phys, want_coords=True, want_det=True, want_jinv=True):
     """geom_dofs[E][n_phys][Ng] -> coords[E][n_phys][1+d][Q], det[E][Q], jinv[E][Q][d][n_phys]"""
     Ng, Q = _counts(geom_basis, rules)

@@ -187,3 +187,21 @@ def basis_points_1d(basis1, x):
     b = ip.BasisSpecs(*basis1)
     x = np.ascontiguousarray(x, dtype=np.float64)
     return np.asarray(b.values(x)).reshape(len(x), -1), np.asarray(b.derivatives(x)).reshape(len(x), -1)
+
+
+def incidence_matrix(basis1):
+    ip = ref()
+    from interplib import _interp  # not re-exported by the package (tests/test_incidence.py:9-13 import it from here)
+
+    return np.asarray(_interp.incidence_matrix(ip.BasisSpecs(*basis1)))
+
+
+def dof_derivative(basis, dofs, idim):
+    """DegreesOfFreedom.derivative(idim) per element: dofs[E][N] -> [E][N_lower]"""
+    ip = ref()
+    fs = _fs(ip, basis)
+    shape = [o + 1 for _, o in basis]
+    dofs = np.asarray(dofs, dtype=np.float64).reshape(-1, int(np.prod(shape)))
+    out = [np.asarray(ip.DegreesOfFreedom(fs, dofs[e].reshape(shape)).derivative(idim).values).reshape(-1)
+           for e in range(dofs.shape[0])]
+    return np.stack(out)

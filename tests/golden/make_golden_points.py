@@ -1,5 +1,6 @@
 #!/usr/bin/env python3
-"""Generate tests/golden/points.npz -- arbitrary-point evaluation by the UNMODIFIED compiled
+"""Generate tests/golden/points.npz and incidence.npz -- arbitrary-point evaluation and
+incidence matrices / derivative DoFs (row N3: incidence_matrix, DegreesOfFreedom.derivative) by the UNMODIFIED compiled
 reference (oracle/_ref): FunctionSpace.evaluate, interplib.reconstruct and BasisSpecs.values/.derivatives on seeded
 random points.  Run in the build container only:  python tests/golden/make_golden_points.py"""
 import sys
@@ -24,6 +25,14 @@ SPACES = {
 }
 
 
+DERIV_SPACES = {
+    "c2": [("lagrange-gauss-lobatto", 6)] * 2,
+    "c3a": [("lagrange-gauss-lobatto", 7), ("lagrange-gauss-lobatto", 8)],
+    "line": [("bernstein", 3)],
+    "mixed3": [("legendre", 4), ("bernstein", 2), ("lagrange-chebyshev-gauss", 3)],
+}
+
+
 def main():
     rng = np.random.default_rng(2024)
     data = {}
@@ -45,6 +54,20 @@ def main():
             data[f"der_{bt}_{order}"] = d
     np.savez(OUT / "points.npz", **data)
     print({k: v.shape for k, v in data.items()})
+
+    # N3: incidence matrices and DegreesOfFreedom.derivative
+    inc = {}
+    for bt in ALL_BASIS:
+        for order in (1, 2, 5, 8, 16):
+            inc[f"inc_{bt}_{order}"] = rd.incidence_matrix((bt, order))
+    for name, basis in DERIV_SPACES.items():
+        N = int(np.prod([o + 1 for _, o in basis]))
+        dofs = rng.standard_normal((4, N))
+        inc[f"{name}_dofs"] = dofs
+        for k in range(len(basis)):
+            inc[f"{name}_d{k}"] = rd.dof_derivative(basis, dofs, k)
+    np.savez(OUT / "incidence.npz", **inc)
+    print({k: v.shape for k, v in inc.items() if not k.startswith("inc_")})
 
 
 if __name__ == "__main__":
