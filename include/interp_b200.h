@@ -283,8 +283,10 @@ IB200_API int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, cons
 
 /* ---- N1 ("next"): batched primal solve M u = b --------------------------------- */
 /* projection_l2_primal, python/interplib/integration.py:171-223 (np.linalg.solve per element).
- * mass[E][N][N] symmetric positive definite (destroyed: overwritten by its Cholesky factor),
- * rhs[E][N] overwritten by the solution. */
+ * mass[E][N][N] symmetric positive definite, lower triangle read; rhs[E][N] overwritten by the solution.
+ * Systems up to N = 127 are factorised in shared memory (matrix read once, left untouched); larger ones
+ * in place in device memory (a DEVICE-resident mass is then overwritten by its Cholesky factor; a HOST
+ * array is never written back). */
 IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
                                     int where);
 

@@ -1295,7 +1295,8 @@ extern "C" int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elem
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "mass/rhs must not be NULL");
     if (n == 0 || n > 4096)
         return ib200_fail(IB200_ERROR_UNSUPPORTED, "system size %u outside 1..4096", n);
-    std::vector<BatchArray> arrays = {{ARR_INOUT, mass, sizeof(double) * n * n}, {ARR_INOUT, rhs, sizeof(double) * n}};
+    // host matrices are not copied back: a host caller's `mass` is left unchanged
+    std::vector<BatchArray> arrays = {{ARR_IN, mass, sizeof(double) * n * n}, {ARR_INOUT, rhs, sizeof(double) * n}};
     return run_batched(ctx, n_elements, arrays, where, 0,
                        [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
                            return launch_spd_solve(cfg, n, cnt, (double *)dev[0], (double *)dev[1]);

@@ -471,6 +471,80 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
     }
 }
 
+// Shared-memory variant for systems that fit (n up to ~100): one warp per element, the matrix is read from global memory
+// ONCE (coalesced), factorised in shared memory and only the solution is written -- 8(n^2 + 2n) bytes per element instead
+// of the read-modify-write traffic of the in-place kernel above.  Left-looking (Crout) Cholesky with the right-hand side
+// appended as row n, so the forward substitution is the same recurrence: at column k the lane owning row i >= k forms
+// s_i = A[i][k] - sum_{m<k} L[i][m] L[k][m] (its own row: stride ld, odd -> conflict-free; the pivot row: broadcast),
+// then L[i][k] = s_i / sqrt(s_k).  Back substitution is column oriented (no reductions).
+__global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size_t E, const double *__restrict__ mass,
+                                                             double *__restrict__ rhs)
+{
+    extern __shared__ __align__(16) double chol_smem[];
+    const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
+    double *L = chol_smem + (size_t)warp_in_cta * (n + 1) * ld;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t e = warp; e < E; e += n_warps)
+    {
+        const double *A = mass + e * (size_t)n * n;
+        double *b = rhs + e * (size_t)n;
+        __syncwarp();
+        for (int idx = lane; idx < n * n; idx += 32)
+        {
+            const int i = idx / n, j = idx - i * n;
+            L[i * ld + j] = __ldcs(A + idx);
+        }
+        for (int j = lane; j < n; j += 32)
+            L[n * ld + j] = b[j];
+        __syncwarp();
+        for (int k = 0; k < n; ++k)
+        {
+            const double *pk = L + k * ld;
+            double s_first = 0.0; // s of the first row this lane owns (row k for lane 0)
+            double sv[4];         // up to 4 rows per lane: n + 1 <= 128
+            int cnt = 0;
+            for (int i = k + lane; i <= n; i += 32, ++cnt)
+            {
+                const double *pi = L + i * ld;
+                double a0 = pi[k], a1 = 0.0, a2 = 0.0, a3 = 0.0;
+                int m = 0;
+                for (; m + 4 <= k; m += 4)
+                {
+                    a0 = fma(-pi[m], pk[m], a0);
+                    a1 = fma(-pi[m + 1], pk[m + 1], a1);
+                    a2 = fma(-pi[m + 2], pk[m + 2], a2);
+                    a3 = fma(-pi[m + 3], pk[m + 3], a3);
+                }
+                for (; m < k; ++m)
+                    a0 = fma(-pi[m], pk[m], a0);
+                sv[cnt] = (a0 + a1) + (a2 + a3);
+                if (cnt == 0)
+                    s_first = sv[0];
+            }
+            const double akk = sqrt(__shfl_sync(0xffffffffu, s_first, 0));
+            cnt = 0;
+            for (int i = k + lane; i <= n; i += 32, ++cnt)
+                L[i * ld + k] = (i == k) ? akk : sv[cnt] / akk;
+            __syncwarp();
+        }
+        // L[n][k] = y_k;  L^T u = y, column oriented: u_k = y_k / L[k][k], then y_i -= L[k][i] u_k for i < k
+        double *y = L + n * ld;
+        for (int k = n - 1; k >= 0; --k)
+        {
+            const double uk = y[k] / L[k * ld + k];
+            __syncwarp();
+            for (int i = lane; i < k; i += 32)
+                y[i] = fma(-L[k * ld + i], uk, y[i]);
+            if (lane == 0)
+                y[k] = uk;
+            __syncwarp();
+        }
+        for (int j = lane; j < n; j += 32)
+            b[j] = y[j];
+    }
+}
+
 // ---- projection norms: deterministic two-pass dot product sum_i a[i]*b[i] (fixed block -> partial mapping) ----
 constexpr int kDotBlocks = 592; // 4 CTAs per SM on 148 SMs
 
@@ -591,6 +665,30 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
         return INTERP_SUCCESS;
     const size_t warps = E;
     size_t blocks = (warps * 32 + 127) / 128;
+    const int ld = (int)n | 1;
+    int wpc = 4; // warps per CTA: as many as 200 KB of shared memory hold
+    while (wpc > 1 && sizeof(double) * wpc * (n + 1) * ld > 200 * 1024)
+        wpc /= 2;
+    const size_t smem = sizeof(double) * wpc * (n + 1) * ld;
+    if (n + 1 <= 128 && smem <= 200 * 1024)
+    {
+        blocks = (warps + wpc - 1) / wpc;
+        // shared-memory resident factorisation (the matrix is left untouched)
+        static bool attr_set = false;
+        if (!attr_set)
+        {
+            IB_CUDA(cudaFuncSetAttribute(spd_solve_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            attr_set = true;
+        }
+        int per_sm = 0;
+        IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_smem_kernel, 32 * wpc, smem));
+        const size_t cap = (size_t)cfg.sm_count * std::max(per_sm, 1);
+        if (blocks > cap)
+            blocks = cap;
+        spd_solve_smem_kernel<<<(int)blocks, 32 * wpc, smem, cfg.stream>>>((int)n, ld, E, mass, rhs);
+        ++*cfg.launch_counter;
+        return check_launch("spd_solve_smem_kernel");
+    }
     const size_t cap = (size_t)cfg.sm_count * 16;
     if (blocks > cap)
         blocks = cap;

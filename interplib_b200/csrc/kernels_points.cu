@@ -239,6 +239,61 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// Tiled variant (the one normally launched): a CTA stages the DoFs of EPB consecutive elements (one contiguous run of
+// global memory) in shared memory with coalesced loads, every thread then forms output values from shared memory with
+// 32-bit index arithmetic and stores them coalesced.  Same additions in the same order as dof_derivative_kernel.
+__global__ void __launch_bounds__(256)
+    dof_derivative_tiled_kernel(int type, int n, int pre, int post, int epb, const double *__restrict__ inc, size_t E,
+                                const double *__restrict__ in, double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double dd_smem[];
+    const int per_in = pre * (n + 1) * post, per_out = pre * n * post;
+    double *tile = dd_smem;                  // [epb][per_in]
+    double *incs = dd_smem + epb * per_in;   // [n][n+1] (Lagrange only)
+    if (inc)
+        for (int i = threadIdx.x; i < n * (n + 1); i += blockDim.x)
+            incs[i] = inc[i];
+    const size_t n_tiles = (E + epb - 1) / epb;
+    const int np = n * post;
+    for (size_t t = blockIdx.x; t < n_tiles; t += gridDim.x)
+    {
+        const size_t e0 = t * epb;
+        const int ne = (int)((E - e0) < (size_t)epb ? (E - e0) : (size_t)epb);
+        const double *src = in + e0 * per_in;
+        __syncthreads(); // previous tile consumed (and incs written)
+        for (int i = threadIdx.x; i < ne * per_in; i += blockDim.x)
+            tile[i] = __ldcs(src + i);
+        __syncthreads();
+        double *dst = out + e0 * per_out;
+        for (int o = threadIdx.x; o < ne * per_out; o += blockDim.x)
+        {
+            const int el = o / per_out, rem = o - el * per_out;
+            const int i_pre = rem / np, r2 = rem - i_pre * np;
+            const int row = r2 / post, i_post = r2 - row * post;
+            const double *sp = tile + el * per_in + i_pre * (n + 1) * post + i_post;
+            double v = 0.0;
+            if (type == BASIS_BERNSTEIN)
+            {
+                const double c = (double)n / 2.0;
+                v = __dadd_rn(__dsub_rn(0.0, __dmul_rn(c, sp[row * post])), __dmul_rn(c, sp[(row + 1) * post]));
+            }
+            else if (type == BASIS_LEGENDRE)
+            {
+                const double w = (double)(2 * row + 1);
+                for (int col = row + 1 + 2 * ((n - row - 1) / 2); col > row; col -= 2)
+                    v = __dadd_rn(v, __dmul_rn(w, sp[col * post]));
+            }
+            else
+            {
+                const double *m = incs + row * (n + 1);
+                for (int col = 0; col <= n; ++col)
+                    v = __dadd_rn(v, __dmul_rn(m[col], sp[col * post]));
+            }
+            __stcs(dst + o, v);
+        }
+    }
+}
+
 } // namespace
 
 int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, size_t post, const double *d_inc, size_t E,
@@ -247,8 +302,22 @@ int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, siz
     const size_t total = E * pre * (size_t)n * post;
     if (total == 0)
         return INTERP_SUCCESS;
-    const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)cfg.sm_count * 8);
-    dof_derivative_kernel<<<grid, 256, 0, cfg.stream>>>(type, n, pre, post, d_inc, E, in, out);
+    const size_t per_in = pre * (size_t)(n + 1) * post;
+    const size_t inc_bytes = d_inc ? sizeof(double) * n * (n + 1) : 0;
+    if (per_in * sizeof(double) + inc_bytes <= 40 * 1024)
+    {
+        // about 24 KB of staged DoFs per CTA (at least one element), 4+ CTAs per SM
+        const int epb = (int)std::max<size_t>(1, std::min<size_t>(24 * 1024 / (per_in * sizeof(double)), 256));
+        const size_t smem = sizeof(double) * epb * per_in + inc_bytes;
+        const size_t n_tiles = (E + epb - 1) / epb;
+        const int grid = (int)std::min<size_t>(n_tiles, (size_t)cfg.sm_count * 6);
+        dof_derivative_tiled_kernel<<<grid, 256, smem, cfg.stream>>>(type, n, (int)pre, (int)post, epb, d_inc, E, in, out);
+    }
+    else
+    {
+        const int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)cfg.sm_count * 8);
+        dof_derivative_kernel<<<grid, 256, 0, cfg.stream>>>(type, n, pre, post, d_inc, E, in, out);
+    }
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)

@@ -1,0 +1,85 @@
+#!/usr/bin/env python3
+"""Device-resident timings of the SURVEY 8f "next" rows (N1 primal solve, N2 arbitrary points, N3 derivative DoFs) on one
+GPU: CUDA events on the context stream, 3 warm-ups, best of 5; prints one JSON line per kernel with the algorithmic
+bytes per element and the achieved fraction of the measured HBM copy bandwidth.   python tools/bench_next.py"""
+import json
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+import interplib_b200 as ib  # noqa: E402
+from interplib_b200 import DEVICE, synthetic as syn  # noqa: E402
+
+
+def peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    return float(json.loads(p.read_text())["hbm_gbs"]) if p.exists() else 6650.0
+
+
+def timed(ctx, fn, reps=5, warm=3, setup=None):
+    best = 1e30
+    for i in range(warm + reps):
+        if setup:
+            setup()
+        ctx.timer_start(2)
+        fn()
+        ctx.timer_stop(2)
+        ms = ctx.timer_ms(2)
+        if i >= warm:
+            best = min(best, ms)
+    return best
+
+
+def report(name, E, bytes_per_el, ms):
+    gbs = bytes_per_el * E / (ms * 1e-3) / 1e9
+    print(json.dumps({"kernel": name, "elements": E, "ms": round(ms, 4), "elements_per_s": E / (ms * 1e-3),
+                      "algorithmic_bytes_per_element": bytes_per_el, "achieved_gbs": round(gbs, 1),
+                      "frac_of_hbm_peak": round(gbs / peak(), 3)}))
+
+
+def main():
+    ctx = ib.Context(0)
+    rng = np.random.default_rng(0)
+    # ---- N1: M u = b for the C5 system (25 x 25), 2^19 elements
+    cfg = syn.CONFIGS["c5"]
+    basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
+    E = 1 << 19
+    geom = syn.geometry(cfg, first=0, count=E)
+    f = rng.standard_normal((E, cfg.Q))
+    d_g, d_f = ctx.alloc(geom.nbytes).upload(geom), ctx.alloc(f.nbytes).upload(f)
+    d_M, d_b = ctx.alloc(E * cfg.N * cfg.N * 8), ctx.alloc(E * cfg.N * 8)
+
+    def assemble():
+        ctx.l2_system_mapped(basis, rules, gb, d_g.ptr, 2, d_f.ptr, mass=d_M.ptr, rhs=d_b.ptr, where=DEVICE, n_elements=E)
+
+    ms = timed(ctx, lambda: ctx.spd_solve(d_M.ptr, d_b.ptr, where=DEVICE, n=cfg.N, n_elements=E), setup=assemble)
+    report("N1 spd_solve 25x25 (read M + b, write u)", E, 8 * (cfg.N * cfg.N + 2 * cfg.N), ms)
+    for b in (d_g, d_f, d_M, d_b):
+        b.free()
+    # ---- N2: reconstruct value + gradient at 64 arbitrary points per element, C2 space, 2^18 elements
+    cfg = syn.CONFIGS["c2"]
+    basis = list(cfg.basis)
+    E, P = 1 << 18, 64
+    u, x = rng.random((E, cfg.N)), rng.uniform(-1, 1, (E, 2, P))
+    d_u, d_x, d_o = ctx.alloc(u.nbytes).upload(u), ctx.alloc(x.nbytes).upload(x), ctx.alloc(E * 3 * P * 8)
+    ms = timed(ctx, lambda: ctx.reconstruct_points(basis, d_u.ptr, d_x.ptr, [0, 1, 2], out=d_o.ptr, where=DEVICE, n_elements=E,
+                                                   n_points=P))
+    report("N2 reconstruct_points p=6, 64 points, value+gradient", E, 8 * (cfg.N + 2 * P + 3 * P), ms)
+    # ---- N3: derivative DoFs along dimension 0 and 1, C2 space, 2^20 elements
+    for b in (d_u, d_x, d_o):
+        b.free()
+    E = 1 << 20
+    u = rng.random((E, cfg.N))
+    d_u, d_o = ctx.alloc(u.nbytes).upload(u), ctx.alloc(E * 42 * 8)
+    for k in range(2):
+        ms = timed(ctx, lambda: ctx.dof_derivative(basis, d_u.ptr, k, out=d_o.ptr, where=DEVICE, n_elements=E))
+        report(f"N3 dof_derivative p=6 along dim {k}", E, 8 * (49 + 42), ms)
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
