@@ -877,8 +877,10 @@ static int ctx_make_point_op(ib200_ctx *ctx, unsigned ndim, const basis_spec_t *
             auto it = ctx->point_tabs.find(key);
             if (it == ctx->point_tabs.end())
             {
-                std::vector<double> h(2 * (size_t)d.n);
+                std::vector<double> h(3 * (size_t)d.n); // roots | denominators | reciprocal denominators
                 IB_TRY(ib200_tables_lagrange_roots_denominators(basis[k], h.data(), h.data() + d.n));
+                for (int j = 0; j < d.n; ++j)
+                    h[2 * (size_t)d.n + j] = 1.0 / h[(size_t)d.n + j];
                 double *dev = nullptr;
                 IB_CUDA(cudaMalloc((void **)&dev, sizeof(double) * h.size()));
                 IB_CUDA(cudaMemcpy(dev, h.data(), sizeof(double) * h.size(), cudaMemcpyHostToDevice));

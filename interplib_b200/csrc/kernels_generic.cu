@@ -674,12 +674,8 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
     {
         blocks = (warps + wpc - 1) / wpc;
         // shared-memory resident factorisation (the matrix is left untouched)
-        static bool attr_set = false;
-        if (!attr_set)
-        {
-            IB_CUDA(cudaFuncSetAttribute(spd_solve_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            attr_set = true;
-        }
+        // per launch, not once per process: the attribute is per device and a process may hold contexts on several
+        IB_CUDA(cudaFuncSetAttribute(spd_solve_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         int per_sm = 0;
         IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_smem_kernel, 32 * wpc, smem));
         const size_t cap = (size_t)cfg.sm_count * std::max(per_sm, 1);

@@ -15,6 +15,7 @@
 // element's DoFs is sum-factorised per point, DoFs are read through the read-only path (the threads of a block share
 // an element).  Not a roofline-tuned kernel: it is the caller-side companion of K1 (sampling geometry, plotting).
 #include <algorithm>
+#include <cstdlib>
 
 #include "ctx.cuh"
 
@@ -197,6 +198,231 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+// ---- cooperative variants (the ones normally launched) ---------------------------------------------------------------
+// A CTA takes one element and a chunk of PB of its points at a time.  Phase 1 tabulates the 1-D values (and derivatives)
+// of every dimension at the chunk's points in shared memory -- one work item per (dimension, point, basis function) for
+// the Lagrange family (the numerator product needs no scratch), per (dimension, point) for the recursions, which write
+// their rows straight to shared memory; same operation order as pt_basis_1d.  Phase 2 contracts: one work item per
+// (point, field) against the element's DoFs (staged in shared memory once per element) / per output entry of the tensor
+// basis.  No per-thread local arrays (the thread-per-point kernels above keep 1.7 KB of them on the stack).
+struct PointTabs
+{
+    int ld[IB200_POINT_MAX_DIM];  // padded row length of a point's table (odd)
+    int off[IB200_POINT_MAX_DIM]; // offset of dimension k's value table in doubles; the derivative table follows it
+    int total;                    // doubles of all tables for PB points
+};
+
+__device__ __forceinline__ PointTabs point_tabs_layout(const PointOp &op, int PB, bool with_der)
+{
+    PointTabs t{};
+    int o = 0;
+    for (int k = 0; k < op.ndim; ++k)
+    {
+        t.ld[k] = op.dim[k].n | 1;
+        t.off[k] = o;
+        o += (with_der ? 2 : 1) * PB * t.ld[k];
+    }
+    t.total = o;
+    return t;
+}
+
+// phase 1 for the points [p0, p0 + np) of element e
+__device__ void point_tabs_fill(const PointOp &op, const PointTabs &lay, int PB, bool with_der, double *tabs, const double *xe,
+                                size_t P, size_t p0, int np)
+{
+    for (int k = 0; k < op.ndim; ++k)
+    {
+        const PointDim &pd = op.dim[k];
+        const int n = pd.n, ld = lay.ld[k];
+        double *val = tabs + lay.off[k], *der = val + PB * ld;
+        const double *xk = xe + (size_t)k * P + p0;
+        if (pd.type == BASIS_LEGENDRE || pd.type == BASIS_BERNSTEIN)
+        {
+            for (int p = threadIdx.x; p < np; p += blockDim.x)
+            {
+                const double x = xk[p];
+                double *v = val + p * ld, *dv = der + p * ld;
+                if (pd.type == BASIS_LEGENDRE)
+                {
+                    v[0] = 1.0;
+                    if (n > 1)
+                        v[1] = x;
+                    double lo = 1.0, hi = x;
+                    for (int i = 2; i < n; ++i)
+                    {
+                        const double a = __dmul_rn((double)(2 * i - 1), x);
+                        const double next = __ddiv_rn(__dsub_rn(__dmul_rn(a, hi), __dmul_rn((double)(i - 1), lo)), (double)i);
+                        v[i] = next;
+                        lo = hi;
+                        hi = next;
+                    }
+                    if (with_der)
+                    {
+                        double d = 0.0;
+                        dv[0] = 0.0;
+                        for (int i = 1; i < n; ++i)
+                        {
+                            d = __dadd_rn(__dmul_rn((double)i, v[i - 1]), __dmul_rn(x, d));
+                            dv[i] = d;
+                        }
+                    }
+                }
+                else
+                {
+                    const double t = __dmul_rn(__dadd_rn(x, 1.0), 0.5);
+                    const double a = __dsub_rn(1.0, t), b = t;
+                    const int deg = n - 1;
+                    // degree deg-1 polynomials in dv (they give the derivative), one more raising step for the values
+                    double *w = with_der ? dv : v;
+                    const int wdeg = with_der ? deg - 1 : deg;
+                    w[0] = 1.0;
+                    for (int i = 0; i < wdeg; ++i)
+                    {
+                        w[i + 1] = __dmul_rn(w[i], b);
+                        for (int j = i; j > 0; --j)
+                            w[j] = __dadd_rn(__dmul_rn(b, w[j - 1]), __dmul_rn(a, w[j]));
+                        w[0] = __dmul_rn(w[0], a);
+                    }
+                    if (with_der)
+                    {
+                        if (deg == 0)
+                        {
+                            v[0] = 1.0;
+                            dv[0] = 0.0;
+                        }
+                        else
+                        {
+                            v[deg] = __dmul_rn(w[deg - 1], b);
+                            for (int j = deg - 1; j > 0; --j)
+                                v[j] = __dadd_rn(__dmul_rn(b, w[j - 1]), __dmul_rn(a, w[j]));
+                            v[0] = __dmul_rn(w[0], a);
+                            // in place, descending: dv[j] needs the old w[j-1] and w[j] only
+                            dv[deg] = __dmul_rn((double)deg, w[deg - 1]);
+                            for (int j = deg - 1; j > 0; --j)
+                                dv[j] = __dmul_rn((double)deg, __dsub_rn(w[j - 1], w[j]));
+                            dv[0] = __dmul_rn(w[0], -(double)deg);
+                            for (int j = 0; j < n; ++j)
+                                dv[j] = __dmul_rn(dv[j], 0.5);
+                        }
+                    }
+                }
+            }
+        }
+        else
+        {
+            for (int item = threadIdx.x; item < np * n; item += blockDim.x)
+            {
+                const int p = item / n, j = item - p * n;
+                const double x = xk[p];
+                double acc = 1.0, dd = 0.0;
+                for (int m = 0; m < n; ++m)
+                {
+                    if (m == j)
+                        continue;
+                    const double dif = __dsub_rn(x, pd.roots[m]);
+                    dd = fma(dd, dif, acc);
+                    acc = __dmul_rn(acc, dif);
+                }
+                // times the host-rounded reciprocal of the denominator (stored after roots and denominators): one
+                // rounding more than the reference's division, a tenth of its instructions
+                const double inv = pd.den[n + j];
+                val[p * ld + j] = n == 1 ? 1.0 : __dmul_rn(acc, inv);
+                if (with_der)
+                    der[p * ld + j] = n == 1 ? 0.0 : __dmul_rn(dd, inv);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+    points_reconstruct_coop_kernel(const PointOp op, int PB, size_t E, size_t P, const double *__restrict__ dofs,
+                                   const double *__restrict__ x, int n_fields, const PointMasks masks, bool any_deriv,
+                                   double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double pt_smem[];
+    const PointTabs lay = point_tabs_layout(op, PB, any_deriv);
+    double *tabs = pt_smem, *c = pt_smem + lay.total;
+    const int n0 = op.dim[0].n, n1 = op.ndim > 1 ? op.dim[1].n : 1, n2 = op.ndim > 2 ? op.dim[2].n : 1;
+    for (size_t e = blockIdx.x; e < E; e += gridDim.x)
+    {
+        __syncthreads();
+        for (int i = threadIdx.x; i < op.N; i += blockDim.x)
+            c[i] = dofs[e * (size_t)op.N + i];
+        const double *xe = x + e * (size_t)op.ndim * P;
+        for (size_t p0 = (size_t)blockIdx.y * PB; p0 < P; p0 += (size_t)PB * gridDim.y)
+        {
+            const int np = (int)((P - p0) < (size_t)PB ? (P - p0) : (size_t)PB);
+            __syncthreads(); // tables of the previous chunk consumed
+            point_tabs_fill(op, lay, PB, any_deriv, tabs, xe, P, p0, np);
+            __syncthreads();
+            for (int item = threadIdx.x; item < np * n_fields; item += blockDim.x)
+            {
+                const int f = item / np, p = item - f * np; // consecutive threads -> consecutive points
+                const unsigned m = masks.m[f];
+                const double *t0 = tabs + lay.off[0] + ((m & 1u) ? PB * lay.ld[0] : 0) + p * lay.ld[0];
+                const double *t1 = op.ndim > 1 ? tabs + lay.off[1] + ((m & 2u) ? PB * lay.ld[1] : 0) + p * lay.ld[1] : nullptr;
+                const double *t2 = op.ndim > 2 ? tabs + lay.off[2] + ((m & 4u) ? PB * lay.ld[2] : 0) + p * lay.ld[2] : nullptr;
+                double acc0 = 0.0;
+                for (int i0 = 0; i0 < n0; ++i0)
+                {
+                    double acc1 = 0.0;
+                    for (int i1 = 0; i1 < n1; ++i1)
+                    {
+                        const double *row = c + (i0 * n1 + i1) * n2;
+                        double acc2 = 0.0;
+                        if (op.ndim > 2)
+                        {
+                            for (int i2 = 0; i2 < n2; ++i2)
+                                acc2 = fma(row[i2], t2[i2], acc2);
+                        }
+                        else
+                            acc2 = row[0];
+                        acc1 = op.ndim > 1 ? fma(acc2, t1[i1], acc1) : acc2;
+                    }
+                    acc0 = fma(acc1, t0[i0], acc0);
+                }
+                out[(e * n_fields + f) * P + p0 + p] = acc0;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+    points_evaluate_coop_kernel(const PointOp op, int PB, size_t E, size_t P, const double *__restrict__ x, double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double pt_smem[];
+    const PointTabs lay = point_tabs_layout(op, PB, false);
+    double *tabs = pt_smem;
+    const int n1 = op.ndim > 1 ? op.dim[1].n : 1, n2 = op.ndim > 2 ? op.dim[2].n : 1, n12 = n1 * n2;
+    for (size_t e = blockIdx.x; e < E; e += gridDim.x)
+    {
+        const double *xe = x + e * (size_t)op.ndim * P;
+        for (size_t p0 = (size_t)blockIdx.y * PB; p0 < P; p0 += (size_t)PB * gridDim.y)
+        {
+            const int np = (int)((P - p0) < (size_t)PB ? (P - p0) : (size_t)PB);
+            __syncthreads();
+            point_tabs_fill(op, lay, PB, false, tabs, xe, P, p0, np);
+            __syncthreads();
+            double *o = out + (e * P + p0) * (size_t)op.N;
+            for (int p = 0; p < np; ++p)
+            {
+                const double *t0 = tabs + lay.off[0] + p * lay.ld[0];
+                const double *t1 = tabs + lay.off[1] + p * lay.ld[1], *t2 = tabs + lay.off[2] + p * lay.ld[2];
+                for (int i = threadIdx.x; i < op.N; i += blockDim.x)
+                {
+                    const int i0 = i / n12, r = i - i0 * n12, i1 = r / n2, i2 = r - i1 * n2;
+                    double v = __dmul_rn(1.0, t0[i0]);
+                    if (op.ndim > 1)
+                        v = __dmul_rn(v, t1[i1]);
+                    if (op.ndim > 2)
+                        v = __dmul_rn(v, t2[i2]);
+                    __stcs(o + (size_t)p * op.N + i, v);
+                }
+            }
+        }
+    }
+}
+
 // N3 -- DegreesOfFreedom.derivative(idim), /root/reference/src/python/degrees_of_freedom.c:738-945: the 1-D incidence
 // operator [n][n+1] (src/python/incidence.c:38-110) applied along one dimension of every element's DoF tensor,
 //   out[e][pre][row][post] = sum_col Inc[row][col] * in[e][pre][col][post].
@@ -250,11 +476,18 @@ __global__ void __launch_bounds__(256)
     const int per_in = pre * (n + 1) * post, per_out = pre * n * post;
     double *tile = dd_smem;                  // [epb][per_in]
     double *incs = dd_smem + epb * per_in;   // [n][n+1] (Lagrange only)
+    int2 *desc = reinterpret_cast<int2 *>(incs + (inc ? n * (n + 1) : 0)); // [per_out] {offset of column 0 in the element, row}
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     if (inc)
         for (int i = threadIdx.x; i < n * (n + 1); i += blockDim.x)
             incs[i] = inc[i];
+    for (int r = threadIdx.x; r < per_out; r += blockDim.x)
+    {
+        const int i_pre = r / (n * post), r2 = r - i_pre * n * post;
+        const int row = r2 / post, i_post = r2 - row * post;
+        desc[r] = make_int2(i_pre * (n + 1) * post + i_post, row);
+    }
     const size_t n_tiles = (E + epb - 1) / epb;
-    const int np = n * post;
     for (size_t t = blockIdx.x; t < n_tiles; t += gridDim.x)
     {
         const size_t e0 = t * epb;
@@ -265,31 +498,36 @@ __global__ void __launch_bounds__(256)
             tile[i] = __ldcs(src + i);
         __syncthreads();
         double *dst = out + e0 * per_out;
-        for (int o = threadIdx.x; o < ne * per_out; o += blockDim.x)
+        // a warp takes whole elements, lane r walks the element's outputs: (source offset, row) of output r come
+        // from the table built once per CTA -> no integer division in the loop
+        for (int el = warp; el < ne; el += n_warps)
         {
-            const int el = o / per_out, rem = o - el * per_out;
-            const int i_pre = rem / np, r2 = rem - i_pre * np;
-            const int row = r2 / post, i_post = r2 - row * post;
-            const double *sp = tile + el * per_in + i_pre * (n + 1) * post + i_post;
-            double v = 0.0;
-            if (type == BASIS_BERNSTEIN)
+            const double *se = tile + el * per_in;
+            for (int r = lane; r < per_out; r += 32)
             {
-                const double c = (double)n / 2.0;
-                v = __dadd_rn(__dsub_rn(0.0, __dmul_rn(c, sp[row * post])), __dmul_rn(c, sp[(row + 1) * post]));
+                const int2 d = desc[r];
+                const double *sp = se + d.x;
+                const int row = d.y;
+                double v = 0.0;
+                if (type == BASIS_BERNSTEIN)
+                {
+                    const double c = (double)n / 2.0;
+                    v = __dadd_rn(__dsub_rn(0.0, __dmul_rn(c, sp[row * post])), __dmul_rn(c, sp[(row + 1) * post]));
+                }
+                else if (type == BASIS_LEGENDRE)
+                {
+                    const double w = (double)(2 * row + 1);
+                    for (int col = row + 1 + 2 * ((n - row - 1) / 2); col > row; col -= 2)
+                        v = __dadd_rn(v, __dmul_rn(w, sp[col * post]));
+                }
+                else
+                {
+                    const double *m = incs + row * (n + 1);
+                    for (int col = 0; col <= n; ++col)
+                        v = __dadd_rn(v, __dmul_rn(m[col], sp[col * post]));
+                }
+                __stcs(dst + el * per_out + r, v);
             }
-            else if (type == BASIS_LEGENDRE)
-            {
-                const double w = (double)(2 * row + 1);
-                for (int col = row + 1 + 2 * ((n - row - 1) / 2); col > row; col -= 2)
-                    v = __dadd_rn(v, __dmul_rn(w, sp[col * post]));
-            }
-            else
-            {
-                const double *m = incs + row * (n + 1);
-                for (int col = 0; col <= n; ++col)
-                    v = __dadd_rn(v, __dmul_rn(m[col], sp[col * post]));
-            }
-            __stcs(dst + o, v);
         }
     }
 }
@@ -304,11 +542,11 @@ int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, siz
         return INTERP_SUCCESS;
     const size_t per_in = pre * (size_t)(n + 1) * post;
     const size_t inc_bytes = d_inc ? sizeof(double) * n * (n + 1) : 0;
-    if (per_in * sizeof(double) + inc_bytes <= 40 * 1024)
+    if (2 * per_in * sizeof(double) + inc_bytes <= 44 * 1024)
     {
         // about 24 KB of staged DoFs per CTA (at least one element), 4+ CTAs per SM
         const int epb = (int)std::max<size_t>(1, std::min<size_t>(24 * 1024 / (per_in * sizeof(double)), 256));
-        const size_t smem = sizeof(double) * epb * per_in + inc_bytes;
+        const size_t smem = sizeof(double) * epb * per_in + inc_bytes + sizeof(int2) * pre * n * post;
         const size_t n_tiles = (E + epb - 1) / epb;
         const int grid = (int)std::min<size_t>(n_tiles, (size_t)cfg.sm_count * 6);
         dof_derivative_tiled_kernel<<<grid, 256, smem, cfg.stream>>>(type, n, (int)pre, (int)post, epb, d_inc, E, in, out);
@@ -325,6 +563,39 @@ int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, siz
     return INTERP_SUCCESS;
 }
 
+// Shape of a cooperative launch: points per chunk (<= 64, shrunk until tables + DoFs fit 96 KB), grid (elements x point
+// chunks, about 8 CTAs per SM in total) and the dynamic shared memory in bytes; 0 -> use the thread-per-point kernel.
+static size_t coop_shape(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, bool with_der, bool with_dofs, int *PB,
+                         dim3 *grid)
+{
+    if (std::getenv("IB200_POINTS_NO_COOP"))
+        return 0;
+    int pb = (int)std::min<size_t>(64, P);
+    auto bytes = [&](int b) {
+        size_t d = with_dofs ? (size_t)op.N : 0;
+        for (int k = 0; k < op.ndim; ++k)
+            d += (size_t)(with_der ? 2 : 1) * b * (op.dim[k].n | 1);
+        return d * sizeof(double);
+    };
+    while (pb > 8 && bytes(pb) > 96 * 1024)
+        pb /= 2;
+    if (bytes(pb) > 96 * 1024)
+        return 0;
+    // per launch, not once per process: the attribute is per device and a process may hold contexts on several
+    if (cudaFuncSetAttribute(points_reconstruct_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) != cudaSuccess ||
+        cudaFuncSetAttribute(points_evaluate_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) != cudaSuccess)
+    {
+        cudaGetLastError();
+        return 0;
+    }
+    const size_t chunks = (P + pb - 1) / pb, want = (size_t)cfg.sm_count * 8;
+    const size_t gx = std::min(E, want);
+    const size_t gy = std::min<size_t>(chunks, std::max<size_t>(1, want / gx));
+    *PB = pb;
+    *grid = dim3((unsigned)gx, (unsigned)std::min<size_t>(gy, 65535));
+    return bytes(pb);
+}
+
 int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out)
 {
     if (E == 0 || P == 0)
@@ -332,9 +603,17 @@ int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, si
     for (int k = 0; k < op.ndim; ++k)
         if (op.dim[k].n > PT_MAXN)
             return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
-    const size_t total = E * P;
-    const int grid = (int)std::min<size_t>((total + 127) / 128, (size_t)cfg.sm_count * 16);
-    points_evaluate_kernel<<<grid, 128, 0, cfg.stream>>>(op, E, P, x, out);
+    int PB = 0;
+    dim3 grid;
+    const size_t smem = coop_shape(cfg, op, E, P, false, false, &PB, &grid);
+    if (smem)
+        points_evaluate_coop_kernel<<<grid, 128, smem, cfg.stream>>>(op, PB, E, P, x, out);
+    else
+    {
+        const size_t total = E * P;
+        const int g1 = (int)std::min<size_t>((total + 127) / 128, (size_t)cfg.sm_count * 16);
+        points_evaluate_kernel<<<g1, 128, 0, cfg.stream>>>(op, E, P, x, out);
+    }
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)
@@ -357,9 +636,17 @@ int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E,
     for (int k = 0; k < op.ndim; ++k)
         if (op.dim[k].n > PT_MAXN)
             return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
-    const unsigned gx = (unsigned)std::min<size_t>((P + 127) / 128, 1024);
-    const unsigned gy = (unsigned)std::min<size_t>(E, std::max<size_t>(1, (size_t)cfg.sm_count * 16 / gx));
-    points_reconstruct_kernel<<<dim3(gx, gy), 128, 0, cfg.stream>>>(op, E, P, dofs, x, (int)n_fields, pm, any_deriv, out);
+    int PB = 0;
+    dim3 grid;
+    const size_t smem = coop_shape(cfg, op, E, P, any_deriv, true, &PB, &grid);
+    if (smem)
+        points_reconstruct_coop_kernel<<<grid, 128, smem, cfg.stream>>>(op, PB, E, P, dofs, x, (int)n_fields, pm, any_deriv, out);
+    else
+    {
+        const unsigned gx = (unsigned)std::min<size_t>((P + 127) / 128, 1024);
+        const unsigned gy = (unsigned)std::min<size_t>(E, std::max<size_t>(1, (size_t)cfg.sm_count * 16 / gx));
+        points_reconstruct_kernel<<<dim3(gx, gy), 128, 0, cfg.stream>>>(op, E, P, dofs, x, (int)n_fields, pm, any_deriv, out);
+    }
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)
