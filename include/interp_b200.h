@@ -222,6 +222,39 @@ IB200_API int ib200_incidence_matrix(basis_spec_t basis, double *out);
 IB200_API int ib200_dof_derivative_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, unsigned idim,
                                          size_t n_elements, const double *dofs, double *out, int where);
 
+/* ---- N4: k-form bookkeeping (host, integers only) ------------------------------- */
+/* covector_basis_t, src/basis/covector_basis.h:21-26 (same bit layout): a wedge product of dx_i
+ * as a bit set plus a sign; dimension 0 is the zero bundle. */
+enum
+{
+    IB200_COVECTOR_MAX_DIM = sizeof(unsigned) * 8
+};
+typedef struct
+{
+    unsigned dimension : 31;
+    unsigned sign : 1;
+    unsigned basis_bits;
+} ib200_covector_t;
+/* covector_basis_make / _rank / _is_zero / _wedge / _hodge / _apply_contra_basis / _determine_order,
+ * src/basis/covector_basis.c:27-158.  ib200_covector_order: 0 before, 1 equal, 2 after, 3 not comparable. */
+IB200_API int ib200_covector_make(unsigned dimension, int sign, unsigned rank, const unsigned *indices, ib200_covector_t *out);
+IB200_API unsigned ib200_covector_rank(ib200_covector_t b);
+IB200_API int ib200_covector_is_zero(ib200_covector_t b);
+IB200_API int ib200_covector_wedge(ib200_covector_t b1, ib200_covector_t b2, ib200_covector_t *out);
+IB200_API int ib200_covector_hodge(ib200_covector_t b, ib200_covector_t *out);
+IB200_API int ib200_covector_apply_contra(ib200_covector_t b, unsigned dim, ib200_covector_t *out);
+IB200_API int ib200_covector_order(ib200_covector_t b1, ib200_covector_t b2);
+/* Components of a k-form in ascending order, the function space of one component (order - 1 along
+ * every dimension it contains), the DoF count of a k-form (differential_form_degrees_of_freedom_count,
+ * src/basis/de_rham_sequence.h:66-110) and per-element DoF offsets (prefix sums, offsets[E+1];
+ * element_collection_form_offsets, src/basis/de_rham_sequence.c:62-88). */
+IB200_API unsigned ib200_kform_component_count(unsigned ndim, unsigned k);
+IB200_API int ib200_kform_components(unsigned ndim, unsigned k, ib200_covector_t *out);
+IB200_API int ib200_kform_component_space(unsigned ndim, const basis_spec_t *basis, ib200_covector_t component,
+                                          basis_spec_t *out);
+IB200_API int ib200_kform_dof_count(unsigned ndim, const basis_spec_t *basis, unsigned k, size_t *count);
+IB200_API int ib200_dof_offsets(size_t n_elements, const size_t *counts, size_t *offsets);
+
 /* ---- A9 (K0): batched element geometry ---------------------------------------------------- */
 /* coordinate_map_new + space_map_new, src/python/mappings.c:8-90, 304-556 with
  * matrix_qr_decompose / matrix_back_substitute (src/operations/matrices.c:15-86, 117-141).

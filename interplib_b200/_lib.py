@@ -29,6 +29,20 @@ class BasisSpec(C.Structure):
     _fields_ = [("type", C.c_int), ("order", C.c_uint)]
 
 
+class Covector(C.Structure):
+    """``ib200_covector_t`` = ``covector_basis_t`` (reference src/basis/covector_basis.h:21-26): the C struct packs
+    ``dimension : 31`` and ``sign : 1`` into its first word (GCC allocates bit fields from the least significant bit)."""
+
+    _fields_ = [("dim_sign", C.c_uint), ("basis_bits", C.c_uint)]
+
+    @classmethod
+    def make(cls, dimension: int, sign: int, bits: int) -> "Covector":
+        return cls((dimension & 0x7FFFFFFF) | ((1 if sign else 0) << 31), bits)
+
+    dimension = property(lambda self: self.dim_sign & 0x7FFFFFFF)
+    sign = property(lambda self: self.dim_sign >> 31)
+
+
 class IntegrationSpec(C.Structure):
     """``integration_spec_t`` (reference src/integration/integration_rules.h:17-21)."""
 
@@ -111,6 +125,18 @@ _PROTOTYPES = {
         C.c_int,
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int],
     ),
+    "ib200_covector_make": (C.c_int, [C.c_uint, C.c_int, C.c_uint, C.POINTER(C.c_uint), C.POINTER(Covector)]),
+    "ib200_covector_rank": (C.c_uint, [Covector]),
+    "ib200_covector_is_zero": (C.c_int, [Covector]),
+    "ib200_covector_wedge": (C.c_int, [Covector, Covector, C.POINTER(Covector)]),
+    "ib200_covector_hodge": (C.c_int, [Covector, C.POINTER(Covector)]),
+    "ib200_covector_apply_contra": (C.c_int, [Covector, C.c_uint, C.POINTER(Covector)]),
+    "ib200_covector_order": (C.c_int, [Covector, Covector]),
+    "ib200_kform_component_count": (C.c_uint, [C.c_uint, C.c_uint]),
+    "ib200_kform_components": (C.c_int, [C.c_uint, C.c_uint, C.POINTER(Covector)]),
+    "ib200_kform_component_space": (C.c_int, [C.c_uint, C.POINTER(BasisSpec), Covector, C.POINTER(BasisSpec)]),
+    "ib200_kform_dof_count": (C.c_int, [C.c_uint, C.POINTER(BasisSpec), C.c_uint, C.POINTER(C.c_size_t)]),
+    "ib200_dof_offsets": (C.c_int, [C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "ib200_geometry_batch": (
         C.c_int,
         [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_size_t, C.c_void_p,

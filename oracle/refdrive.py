@@ -205,3 +205,28 @@ def dof_derivative(basis, dofs, idim):
     out = [np.asarray(ip.DegreesOfFreedom(fs, dofs[e].reshape(shape)).derivative(idim).values).reshape(-1)
            for e in range(dofs.shape[0])]
     return np.stack(out)
+
+
+def covector_table(n):
+    """Exhaustive integer table of the reference's CovectorBasis in n dimensions (N4): for every pair of component sets
+    (c1, c2): the wedge's (is_zero, sign, rank), for every c1 its Hodge's sign, and the order relation of equal-rank pairs."""
+    from itertools import combinations
+
+    ref()  # puts oracle/_ref on sys.path
+    from interplib import _interp
+
+    sets = [c for k in range(n + 1) for c in combinations(range(n), k)]
+    full = _interp.CovectorBasis(n, *range(n))
+    wedge, hodge, order = [], [], []
+    for c1 in sets:
+        b1 = _interp.CovectorBasis(n, *c1)
+        h = ~b1
+        # the complement's components are determined; its sign is what has to match: b1 ^ ~b1 == +-full
+        hodge.append([h.rank, h.sign, (b1 ^ h).sign if (b1 ^ h) else 0, 1 if (b1 ^ h) and abs((b1 ^ h).sign) == 1 and (b1 ^ h).rank == full.rank else 0])
+        for c2 in sets:
+            b2 = _interp.CovectorBasis(n, *c2)
+            w = b1 ^ b2
+            wedge.append([1 if w else 0, w.sign if w else 0, w.rank if w else 0])
+            if len(c1) == len(c2):
+                order.append([int(b1 < b2), int(b1 == b2), int(b1 > b2)])
+    return dict(sets=[list(c) for c in sets], wedge=np.array(wedge), hodge=np.array(hodge), order=np.array(order))
