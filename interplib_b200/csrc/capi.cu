@@ -657,7 +657,10 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
         if (scratch_per_elem)
         {
             const size_t budget = (size_t)512 << 20;
-            chunk = std::max<size_t>(1024, budget / scratch_per_elem);
+            // a multiple of 1024 elements: sub-launches must start on the 16-byte (bulk copy) and tile boundaries the
+            // specialised kernels need -- an odd chunk (512 MB / 288 B = 1 864 135 elements) sent every launch after
+            // the first to the generic kernels (C5 shape: 2^21 elements took 8.5 ms instead of 1.6 ms)
+            chunk = std::max<size_t>(1024, (budget / scratch_per_elem) & ~(size_t)1023);
             if (max_device_chunk)
                 chunk = std::min(chunk, max_device_chunk);
             chunk = std::min(chunk, E);
