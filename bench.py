@@ -37,10 +37,10 @@ from interplib_b200 import synthetic as syn  # noqa: E402
 # bench line scales it to the elements of its own launch.  Slightly below the algorithmic bytes where the tail of the
 # output is still dirty in the 126 MB L2 when the kernel ends.
 NCU_TRAFFIC_BYTES = {
-    "c2": (1970035944, 1 << 20),   # profiles/r01d_c2_eval2d_full.txt
+    "c2": (1970064432, 1 << 20),   # profiles/r01e_c2_eval2d_full.txt
     "c5": (5249943208, 1 << 20),   # profiles/r01c_c5_mass2d_lo_full.txt
-    "c4": (5415202552, 1 << 13),   # profiles/r01_c4_mass2d_mma_full.txt
-    "c3": (1415508904, 1 << 15),   # profiles/r01d_c3_mass2d_full.txt
+    "c4": (43748198408, 1 << 16),  # profiles/r01e_c4_mass2d_mma_full.txt
+    "c3": (11733279000, 1 << 18),  # profiles/r01e_c3_mass2d_full.txt
     "c1": None,
 }
 
@@ -108,9 +108,16 @@ class Workload:
         self.d_out = {k: ctx.alloc(int(np.prod(s)) * 8) for k, s in self.out_shapes.items()}
 
     def default_elements(self) -> int:
-        # the whole configuration when its outputs fit comfortably in HBM, else a 2^20-element slab (C5: 16M quads
-        # x 5 kB = 84 GB is executed in slabs; C3/C4 outputs are 43 GB -> 2^15-element slabs)
-        return {"c1": 1024, "c2": 1 << 20, "c3": 1 << 15, "c4": 1 << 13, "c5": 1 << 20}[self.name]
+        # the whole configuration per launch (C3: 2^18 elements, four 10.9 GB blocks; C4: 2^16 elements, 43.8 GB); C5's
+        # 16M quads x 5 kB = 84 GB are executed in slabs of 2^22 elements reusing one output slab
+        return {"c1": 1024, "c2": 1 << 20, "c3": 1 << 18, "c4": 1 << 16, "c5": 1 << 22}[self.name]
+
+    @property
+    def E2(self) -> int:
+        """Elements of one end-to-end step: the host-pointer path streams its arrays through PCIe in 16 MB chunks, so its
+        rate does not depend on the batch; C3-C5 use a slab of the device-resident batch to bound pinned host memory
+        (C3's four blocks of 2^18 elements would be 43 GB of pinned buffers)."""
+        return min(self.E, {"c3": 1 << 15, "c4": 1 << 13, "c5": 1 << 20}.get(self.name, self.E))
 
     def step_device(self, dominant_only: bool = False) -> None:
         from interplib_b200 import DEVICE
@@ -136,10 +143,11 @@ class Workload:
     # end to end through the public host-pointer API (pinned host buffers, H2D + D2H inside the call)
     def e2e_prepare(self) -> None:
         c = self.ctx
-        self.p_in = {k: c.pinned(v.shape) for k, v in self.h_in.items()}
+        n = self.E2
+        self.p_in = {k: c.pinned((n,) + v.shape[1:]) for k, v in self.h_in.items()}
         for k, v in self.h_in.items():
-            self.p_in[k].array[...] = v
-        self.p_out = {k: c.pinned(s) for k, s in self.out_shapes.items()}
+            self.p_in[k].array[...] = v[:n]
+        self.p_out = {k: c.pinned((n,) + tuple(s[1:])) for k, s in self.out_shapes.items()}
 
     def step_e2e(self) -> float:
         c = self.ctx
@@ -156,11 +164,11 @@ class Workload:
 
     @property
     def h2d_bytes(self) -> int:
-        return int(sum(v.nbytes for v in self.h_in.values()))
+        return int(sum(v.nbytes // self.E * self.E2 for v in self.h_in.values()))
 
     @property
     def d2h_bytes(self) -> int:
-        return int(sum(int(np.prod(s)) * 8 for s in self.out_shapes.values()))
+        return int(sum(int(np.prod(s[1:])) * 8 * self.E2 for s in self.out_shapes.values()))
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -446,15 +454,17 @@ def main() -> int:
     ctx.timer_stop(1)
     dom_launches = ctx.stats()["kernel_launches"] - launches_before
     kernel_ms = ctx.timer_ms(1) / max(dom_launches, 1)
-    achieved = wl.dominant_bytes_per_elem * wl.E / (kernel_ms * 1e-3) / 1e9
+    # a device-resident call larger than the context's scratch bound runs as several launches (C5: 1 863 680 elements each)
+    el_per_launch = wl.E * n_dom / max(dom_launches, 1)
+    achieved = wl.dominant_bytes_per_elem * el_per_launch / (kernel_ms * 1e-3) / 1e9
     traffic = NCU_TRAFFIC_BYTES.get(args.workload)
     if traffic is not None:
-        traffic = int(round(traffic[0] * (wl.E / traffic[1])))
+        traffic = int(round(traffic[0] * (el_per_launch / traffic[1])))
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "traffic": traffic, "peak_source": peak_src, "kernel": wl.dominant,
                 "algorithmic_bytes_per_element": wl.dominant_bytes_per_elem, "step_algorithmic_bytes_per_element": wl.bytes_per_elem,
                 "step_frac": wl.bytes_per_elem * wl.E / (ms_step * 1e-3) / 1e9 / hbm_peak,
-                "elements_per_launch": wl.E, "kernel_ms": kernel_ms,
+                "elements_per_launch": el_per_launch, "kernel_ms": kernel_ms,
                 "fp64_flops_per_element": getattr(wl, "flops_per_elem", None)}
 
     # ---- end to end through the host-pointer API (pinned host buffers) -----------------------------------------
@@ -469,8 +479,9 @@ def main() -> int:
             wl.step_e2e()
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": wl.E * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
+        e2e = {"value": wl.E2 * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
                "d2h_bytes_per_step": wl.d2h_bytes, "steps": n_e2e, "ms_per_step": 1e3 * dt / n_e2e,
+               "elements_per_step": wl.E2,
                "timing": "host wall clock around the synchronous C-ABI call, max over ranks"}
 
     # ---- CPU baseline beside it (rank 0, N=1 only) -----------------------------------------------------------------
