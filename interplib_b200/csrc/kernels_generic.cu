@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
 // of the read-modify-write traffic of the in-place kernel above.  Left-looking (Crout) Cholesky with the right-hand side
 // appended as row n, so the forward substitution is the same recurrence: at column k the lane owning row i >= k forms
 // s_i = A[i][k] - sum_{m<k} L[i][m] L[k][m] (its own row: stride ld, odd -> conflict-free; the pivot row: broadcast),
-// then L[i][k] = s_i / sqrt(s_k).  Back substitution is column oriented (no reductions).
+// then L[i][k] = s_i * rsqrt(s_k).  Back substitution is column oriented (no reductions).
 __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size_t E, const double *__restrict__ mass,
                                                              double *__restrict__ rhs)
 {
@@ -490,9 +490,10 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
         const double *A = mass + e * (size_t)n * n;
         double *b = rhs + e * (size_t)n;
         __syncwarp();
-        for (int idx = lane; idx < n * n; idx += 32)
+        for (int idx = lane, i = 0, j = lane; idx < n * n; idx += 32, j += 32)
         {
-            const int i = idx / n, j = idx - i * n;
+            while (j >= n)
+                j -= n, ++i;
             L[i * ld + j] = __ldcs(A + idx);
         }
         for (int j = lane; j < n; j += 32)
@@ -522,17 +523,19 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
                 if (cnt == 0)
                     s_first = sv[0];
             }
-            const double akk = sqrt(__shfl_sync(0xffffffffu, s_first, 0));
+            // one reciprocal square root per column instead of a square root and a division per row (both are long
+            // software sequences in FP64); the diagonal keeps 1 / L[k][k], which is all the substitutions need
+            const double rkk = rsqrt(__shfl_sync(0xffffffffu, s_first, 0));
             cnt = 0;
             for (int i = k + lane; i <= n; i += 32, ++cnt)
-                L[i * ld + k] = (i == k) ? akk : sv[cnt] / akk;
+                L[i * ld + k] = (i == k) ? rkk : sv[cnt] * rkk;
             __syncwarp();
         }
         // L[n][k] = y_k;  L^T u = y, column oriented: u_k = y_k / L[k][k], then y_i -= L[k][i] u_k for i < k
         double *y = L + n * ld;
         for (int k = n - 1; k >= 0; --k)
         {
-            const double uk = y[k] / L[k * ld + k];
+            const double uk = y[k] * L[k * ld + k];
             __syncwarp();
             for (int i = lane; i < k; i += 32)
                 y[i] = fma(-L[k * ld + i], uk, y[i]);
@@ -543,6 +546,122 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
         for (int j = lane; j < n; j += 32)
             b[j] = y[j];
     }
+}
+
+// Register-resident variant for n <= 32 (every 2-D space up to p = 4, 3-D up to p = 2 -- BASELINE config 5 is 25 x 25):
+// one warp per element, lane i holds row i of the lower triangle in registers (all loops unrolled at compile time, so the
+// indices are static).  Right-looking factorisation: at column k the pivot is broadcast by one shuffle, ONE reciprocal
+// square root scales the column, the scaled column goes to shared memory (row k of L^T, later read by the back
+// substitution with unit stride) and comes back as warp-uniform broadcasts for the rank-1 update of the trailing rows
+// a[j] -= l_ik * l_jk.  The forward substitution rides along (b is one more register).  About 1/5 of the instructions of
+// the shared-memory kernel above, which spends most of its issue slots on loop control and the FP64 division routine.
+template <int N>
+__global__ void __launch_bounds__(128) spd_solve_reg_kernel(size_t E, const double *__restrict__ mass, double *__restrict__ rhs)
+{
+    constexpr int LD = N | 1, PANEL = (N * LD + 1) & ~1; // doubles; panels stay 16-byte aligned
+    extern __shared__ __align__(16) double chol_reg_smem[]; // [4 warps][2 panels][PANEL]
+    const int lane = threadIdx.x & 31;
+    double *panels = chol_reg_smem + (size_t)(threadIdx.x >> 5) * 2 * PANEL;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    const int row = lane < N ? lane : N - 1; // idle lanes shadow the last row (their results are never stored)
+    // the matrix of the NEXT element streams into the other panel (cp.async, 8 bytes per lane and request: an element
+    // starts only 8-byte aligned when N is odd) while this one is factorised
+    auto stage = [&](size_t e, double *P) {
+        const double *A = mass + e * (size_t)(N * N);
+        for (int idx = lane, i = 0, j = lane; idx < N * N; idx += 32, j += 32)
+        {
+            while (j >= N)
+                j -= N, ++i;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(P + i * LD + j)),
+                         "l"(A + idx)
+                         : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (warp < E)
+        stage(warp, panels);
+    int cur = 0;
+    for (size_t e = warp; e < E; e += n_warps, cur ^= 1)
+    {
+        double *S = panels + cur * PANEL;
+        double *b = rhs + e * (size_t)N;
+        double y = b[row];
+        __syncwarp(); // every lane is done with the other panel (back substitution of the previous element)
+        if (e + n_warps < E)
+        {
+            stage(e + n_warps, panels + (cur ^ 1) * PANEL);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        }
+        else
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        double a[N];
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+            a[j] = S[row * LD + j];
+        __syncwarp();
+        double rinv = 0.0; // 1 / L[lane][lane]
+#pragma unroll
+        for (int k = 0; k < N; ++k)
+        {
+            const double r = rsqrt(__shfl_sync(0xffffffffu, a[k], k));
+            a[k] *= r; // l_ik for the lanes i >= k (lane k: sqrt of the pivot)
+            const double yk = __shfl_sync(0xffffffffu, y, k) * r;
+            if (lane == k)
+                y = yk, rinv = r;
+            else if (lane > k)
+                y = fma(-a[k], yk, y);
+            if (k + 1 < N)
+            {
+                if (lane < N)
+                    S[k * LD + lane] = a[k];
+                __syncwarp();
+                // rank-1 update of the trailing rows, a[j] -= l_ik l_jk (touches only entries that are still live for
+                // the lanes i >= j); l_jk comes back as warp-uniform broadcasts, two per load where the address is
+                // 16-byte aligned: k LD + k + 2 is even because LD is odd
+                const double *c = S + k * LD;
+                a[k + 1] = fma(-a[k], c[k + 1], a[k + 1]);
+#pragma unroll
+                for (int j = k + 2; j + 1 < N; j += 2)
+                {
+                    const double2 l = *reinterpret_cast<const double2 *>(c + j);
+                    a[j] = fma(-a[k], l.x, a[j]);
+                    a[j + 1] = fma(-a[k], l.y, a[j + 1]);
+                }
+                if (k + 2 < N && ((N - k) & 1))
+                    a[N - 1] = fma(-a[k], c[N - 1], a[N - 1]);
+            }
+        }
+        // L^T u = y, column oriented: u_k = y_k / l_kk, then y_i -= l_ki u_k for i < k (l_ki = S[i][k]: odd stride LD,
+        // conflict free); the lanes i > k already hold u_i
+        __syncwarp();
+#pragma unroll
+        for (int k = N - 1; k >= 0; --k)
+        {
+            const double uk = __shfl_sync(0xffffffffu, y * rinv, k);
+            if (lane == k)
+                y = uk;
+            else if (lane < k)
+                y = fma(-S[lane * LD + k], uk, y);
+        }
+        if (lane < N)
+            b[lane] = y;
+    }
+}
+
+template <int N>
+static void launch_spd_solve_reg(const LaunchCfg &cfg, size_t E, const double *mass, double *rhs)
+{
+    constexpr int LD = N | 1, PANEL = (N * LD + 1) & ~1;
+    const int smem = (int)sizeof(double) * 4 * 2 * PANEL;
+    if (smem > 48 * 1024) // per launch: the attribute is per device
+        cudaFuncSetAttribute(spd_solve_reg_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_reg_kernel<N>, 128, smem) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    const size_t blocks = std::min<size_t>((E + 3) / 4, (size_t)cfg.sm_count * per_sm);
+    spd_solve_reg_kernel<N><<<(int)blocks, 128, smem, cfg.stream>>>(E, mass, rhs);
 }
 
 // ---- projection norms: deterministic two-pass dot product sum_i a[i]*b[i] (fixed block -> partial mapping) ----
@@ -663,6 +782,24 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
 {
     if (E == 0 || n == 0)
         return INTERP_SUCCESS;
+    if (n <= 32 && !getenv("IB200_SPD_NO_REG"))
+    {
+#define IB_SPD_CASE(NN)                                                                                                         \
+    case NN:                                                                                                                    \
+        launch_spd_solve_reg<NN>(cfg, E, mass, rhs);                                                                             \
+        break;
+        switch (n)
+        {
+            IB_SPD_CASE(1) IB_SPD_CASE(2) IB_SPD_CASE(3) IB_SPD_CASE(4) IB_SPD_CASE(5) IB_SPD_CASE(6) IB_SPD_CASE(7) IB_SPD_CASE(8)
+            IB_SPD_CASE(9) IB_SPD_CASE(10) IB_SPD_CASE(11) IB_SPD_CASE(12) IB_SPD_CASE(13) IB_SPD_CASE(14) IB_SPD_CASE(15)
+            IB_SPD_CASE(16) IB_SPD_CASE(17) IB_SPD_CASE(18) IB_SPD_CASE(19) IB_SPD_CASE(20) IB_SPD_CASE(21) IB_SPD_CASE(22)
+            IB_SPD_CASE(23) IB_SPD_CASE(24) IB_SPD_CASE(25) IB_SPD_CASE(26) IB_SPD_CASE(27) IB_SPD_CASE(28) IB_SPD_CASE(29)
+            IB_SPD_CASE(30) IB_SPD_CASE(31) IB_SPD_CASE(32)
+        }
+#undef IB_SPD_CASE
+        ++*cfg.launch_counter;
+        return check_launch("spd_solve_reg_kernel");
+    }
     const size_t warps = E;
     size_t blocks = (warps * 32 + 127) / 128;
     const int ld = (int)n | 1;

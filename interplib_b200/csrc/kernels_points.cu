@@ -15,6 +15,7 @@
 // element's DoFs is sum-factorised per point, DoFs are read through the read-only path (the threads of a block share
 // an element).  Not a roofline-tuned kernel: it is the caller-side companion of K1 (sampling geometry, plotting).
 #include <algorithm>
+#include <cstdint>
 #include <cstdlib>
 
 #include "ctx.cuh"
@@ -532,6 +533,177 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// Column variant (orders up to kDerivColsMax, the one normally launched): a work item is one (element, pre, post) LINE of
+// the DoF tensor -- a thread reads the n+1 values of the line from the staged input tile into registers ONCE, forms all n
+// derivative DoFs from them (incidence row from shared memory, a warp-uniform broadcast; loops unrolled at compile time)
+// and writes them to a staged output tile.  Tiles are contiguous runs of global memory, so they move as ONE bulk async
+// copy each way (cp.async.bulk: mbarrier completion inbound, bulk group outbound), double buffered: the load of tile
+// i+1 and the store of tile i-1 are in flight while tile i is computed.  The additions and their order are those of the
+// kernels above, so the result is bit-identical.
+constexpr int kDerivColsMax = 12;
+constexpr int kDerivColsThreads = 128;
+
+__device__ __forceinline__ unsigned dd_smem_u32(const void *p)
+{
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void dd_mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "DD_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DD_DONE;\n"
+        "bra DD_WAIT;\n"
+        "DD_DONE:\n"
+        "}\n" ::"r"(dd_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void dd_load_tile(double *dst, const double *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dd_smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dd_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(dd_smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void dd_store_tile(double *gdst, const double *ssrc, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(dd_smem_u32(ssrc)), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+// all lines of `ne` staged elements: tin [ne][per_in] -> tout [ne][per_out].  (Two lines per thread, to share the incidence
+// loads, was measured slower: 74 registers and more shared-memory conflicts, 0.59 instead of 0.89 of the HBM roofline.)
+template <int NN>
+__device__ __forceinline__ void deriv_cols_tile(int type, int post, int n_lines, const int2 *desc, const double *incs,
+                                                const double *tin, double *tout)
+{
+    for (int it = threadIdx.x; it < n_lines; it += blockDim.x)
+    {
+        const int2 d = desc[it];
+        const double *sp = tin + d.x;
+        double *op = tout + d.y;
+        double x[NN + 1];
+#pragma unroll
+        for (int c = 0; c <= NN; ++c)
+            x[c] = sp[c * post];
+        if (type == BASIS_BERNSTEIN)
+        {
+            const double c = (double)NN / 2.0;
+#pragma unroll
+            for (int row = 0; row < NN; ++row)
+                op[row * post] = __dadd_rn(__dsub_rn(0.0, __dmul_rn(c, x[row])), __dmul_rn(c, x[row + 1]));
+        }
+        else if (type == BASIS_LEGENDRE)
+        {
+#pragma unroll
+            for (int row = 0; row < NN; ++row)
+            {
+                const double w = (double)(2 * row + 1);
+                double v = 0.0;
+#pragma unroll
+                for (int col = row + 1 + 2 * ((NN - row - 1) / 2); col > row; col -= 2)
+                    v = __dadd_rn(v, __dmul_rn(w, x[col]));
+                op[row * post] = v;
+            }
+        }
+        else
+        {
+#pragma unroll
+            for (int row = 0; row < NN; ++row)
+            {
+                const double *m = incs + row * (NN + 1);
+                double v = 0.0;
+#pragma unroll
+                for (int col = 0; col <= NN; ++col)
+                    v = __dadd_rn(v, __dmul_rn(m[col], x[col]));
+                op[row * post] = v;
+            }
+        }
+    }
+}
+
+// epb is chosen by the launcher so that a full tile starts 16-byte aligned and is a multiple of 16 bytes both ways
+template <int NN>
+__global__ void __launch_bounds__(kDerivColsThreads)
+    dof_derivative_cols_kernel(int type, int pre, int post, int epb, const double *__restrict__ inc, size_t E,
+                               const double *__restrict__ in, double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double dd_smem[];
+    const int lines = pre * post, per_in = lines * (NN + 1), per_out = lines * NN;
+    const int in_tile = (epb * per_in + 1) & ~1, out_tile = (epb * per_out + 1) & ~1; // doubles, 16-byte multiples
+    double *tin = dd_smem;                  // [2][in_tile]
+    double *tout = tin + 2 * in_tile;       // [2][out_tile]
+    double *incs = tout + 2 * out_tile;     // [NN][NN+1] (Lagrange only)
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(incs + (inc ? NN * (NN + 1) : 0)); // [2]
+    int2 *desc = reinterpret_cast<int2 *>(bars + 2); // [epb * lines] {first input, first output} of a line
+    if (threadIdx.x == 0)
+    {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(dd_smem_u32(bars)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(dd_smem_u32(bars + 1)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (inc)
+        for (int i = threadIdx.x; i < NN * (NN + 1); i += blockDim.x)
+            incs[i] = inc[i];
+    for (int it = threadIdx.x; it < epb * lines; it += blockDim.x)
+    {
+        const int el = it / lines, rem = it - el * lines;
+        const int i_pre = rem / post, i_post = rem - i_pre * post;
+        desc[it] = make_int2(el * per_in + i_pre * (NN + 1) * post + i_post, el * per_out + i_pre * NN * post + i_post);
+    }
+    __syncthreads();
+    const size_t n_full = E / epb; // full tiles go through the bulk-copy pipeline
+    const unsigned in_bytes = (unsigned)(epb * per_in * sizeof(double)), out_bytes = (unsigned)(epb * per_out * sizeof(double));
+    if (threadIdx.x == 0 && blockIdx.x < n_full)
+        dd_load_tile(tin, in + (size_t)blockIdx.x * epb * per_in, in_bytes, bars);
+    int i = 0;
+    for (size_t t = blockIdx.x; t < n_full; t += gridDim.x, ++i)
+    {
+        const int cur = i & 1;
+        if (threadIdx.x == 0)
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); // the store that last used tout[cur] has read it
+        __syncthreads(); // ... and every thread is done with tin[cur ^ 1] (tile i - 1)
+        if (threadIdx.x == 0 && t + gridDim.x < n_full)
+            dd_load_tile(tin + (cur ^ 1) * in_tile, in + (t + gridDim.x) * epb * per_in, in_bytes, bars + (cur ^ 1));
+        dd_mbar_wait(bars + cur, (unsigned)(i >> 1) & 1u);
+        deriv_cols_tile<NN>(type, post, epb * lines, desc, incs, tin + cur * in_tile, tout + cur * out_tile);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0)
+            dd_store_tile(out + t * epb * per_out, tout + cur * out_tile, out_bytes);
+    }
+    if (threadIdx.x == 0)
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    // the ragged tail (E % epb elements) with plain loads and stores, by the last CTA
+    const int ne = (int)(E - n_full * epb);
+    if (ne > 0 && blockIdx.x == gridDim.x - 1)
+    {
+        __syncthreads();
+        const double *src = in + n_full * epb * per_in;
+        double *dst = out + n_full * epb * per_out;
+        for (int k = threadIdx.x; k < ne * per_in; k += blockDim.x)
+            tin[k] = src[k];
+        __syncthreads();
+        deriv_cols_tile<NN>(type, post, ne * lines, desc, incs, tin, tout);
+        __syncthreads();
+        for (int k = threadIdx.x; k < ne * per_out; k += blockDim.x)
+            dst[k] = tout[k];
+    }
+}
+
+template <int NN>
+static void launch_deriv_cols(const LaunchCfg &cfg, int grid, size_t smem, int type, int pre, int post, int epb, const double *d_inc,
+                              size_t E, const double *in, double *out)
+{
+    if (smem > 48 * 1024) // per launch: the attribute is per device
+        cudaFuncSetAttribute(dof_derivative_cols_kernel<NN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    dof_derivative_cols_kernel<NN><<<grid, kDerivColsThreads, smem, cfg.stream>>>(type, pre, post, epb, d_inc, E, in, out);
+}
+
 } // namespace
 
 int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, size_t post, const double *d_inc, size_t E,
@@ -542,7 +714,40 @@ int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, siz
         return INTERP_SUCCESS;
     const size_t per_in = pre * (size_t)(n + 1) * post;
     const size_t inc_bytes = d_inc ? sizeof(double) * n * (n + 1) : 0;
-    if (2 * per_in * sizeof(double) + inc_bytes <= 44 * 1024)
+    const size_t lines = pre * post, per_out = lines * n;
+    const size_t el_bytes = sizeof(double) * 2 * (per_in + per_out) + sizeof(int2) * lines; // two buffers each way + line table
+    const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 15u) == 0;
+    if (n <= kDerivColsMax && aligned && 2 * el_bytes + inc_bytes <= 56 * 1024 && !getenv("IB200_DERIV_NO_COLS"))
+    {
+        // elements per tile: an EVEN count (tiles then start 16-byte aligned and are 16-byte multiples whatever per_in is),
+        // 20 .. 52 KB of shared memory per CTA, chosen so that the lines of a tile fill whole passes of the CTA
+        const int lo = (int)std::max<size_t>(2, (20 * 1024 / el_bytes) & ~(size_t)1);
+        const int hi = (int)std::max<size_t>(lo, (52 * 1024 / el_bytes) & ~(size_t)1);
+        int epb = lo;
+        double best = 0.0;
+        for (int c = lo; c <= hi; c += 2)
+        {
+            const size_t items = (size_t)c * lines, passes = (items + kDerivColsThreads - 1) / kDerivColsThreads;
+            const double eff = (double)items / (double)(passes * kDerivColsThreads);
+            if (eff > best + 1e-9)
+                best = eff, epb = c;
+        }
+        const size_t smem = (size_t)epb * el_bytes + inc_bytes + 64;
+        const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(16, 216 * 1024 / (smem + 1024)));
+        const size_t n_tiles = (E + epb - 1) / epb;
+        const int grid = (int)std::min<size_t>(n_tiles, (size_t)cfg.sm_count * per_sm);
+#define IB_DERIV_CASE(NN)                                                                                                       \
+    case NN:                                                                                                                    \
+        launch_deriv_cols<NN>(cfg, grid, smem, type, (int)pre, (int)post, epb, d_inc, E, in, out);                               \
+        break;
+        switch (n)
+        {
+            IB_DERIV_CASE(1) IB_DERIV_CASE(2) IB_DERIV_CASE(3) IB_DERIV_CASE(4) IB_DERIV_CASE(5) IB_DERIV_CASE(6)
+            IB_DERIV_CASE(7) IB_DERIV_CASE(8) IB_DERIV_CASE(9) IB_DERIV_CASE(10) IB_DERIV_CASE(11) IB_DERIV_CASE(12)
+        }
+#undef IB_DERIV_CASE
+    }
+    else if (2 * per_in * sizeof(double) + inc_bytes <= 44 * 1024)
     {
         // about 24 KB of staged DoFs per CTA (at least one element), 4+ CTAs per SM
         const int epb = (int)std::max<size_t>(1, std::min<size_t>(24 * 1024 / (per_in * sizeof(double)), 256));
