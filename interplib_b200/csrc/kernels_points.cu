@@ -388,6 +388,162 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+// 2-D Lagrange-family spaces with at most 8 basis functions per dimension (every BASELINE configuration): ONE
+// THREAD PER POINT, everything in registers with compile-time shapes and unrolled loops -- the 1-D values and derivatives
+// of both dimensions (same operations in the same order as point_tabs_fill), then the contraction in the order of the
+// kernels above (inner sum over i1 for every i0, then over i0), so the result is bit-identical to theirs.  The inner sums
+// with the values and with the derivatives of dimension 1 are formed once and shared by every requested field.  The
+// DoFs of the TE elements a CTA pass covers sit in shared memory (a warp-uniform broadcast when P is a multiple of 32).
+// About 1/12 of the instructions per point of the cooperative kernel, whose run-time loops and shared-memory tables
+// made it issue-bound.
+constexpr int kPtRegThreads = 128;
+
+template <int N>
+__device__ __forceinline__ void pt_lagrange_reg(const double *__restrict__ roots, const double *__restrict__ inv, double x,
+                                                bool with_der, double (&val)[N], double (&der)[N])
+{
+    double dif[N];
+#pragma unroll
+    for (int m = 0; m < N; ++m)
+        dif[m] = __dsub_rn(x, roots[m]);
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+    {
+        double acc = 1.0, dd = 0.0;
+#pragma unroll
+        for (int m = 0; m < N; ++m)
+            if (m != j)
+            {
+                dd = fma(dd, dif[m], acc);
+                acc = __dmul_rn(acc, dif[m]);
+            }
+        val[j] = N == 1 ? 1.0 : __dmul_rn(acc, inv[j]);
+        der[j] = (N == 1 || !with_der) ? 0.0 : __dmul_rn(dd, inv[j]);
+    }
+}
+
+template <int N0, int N1>
+__global__ void __launch_bounds__(kPtRegThreads)
+    points_reconstruct_reg2d_kernel(const PointOp op, int TE, size_t E, size_t P, const double *__restrict__ dofs,
+                                    const double *__restrict__ x, int n_fields, const PointMasks masks, double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double pt_smem[];
+    constexpr int N = N0 * N1;
+    double *r0 = pt_smem, *v0 = r0 + N0, *r1 = v0 + N0, *v1 = r1 + N1; // roots | 1/denominators, per dimension
+    double *c = v1 + N1;                                               // [TE][N]
+    __shared__ unsigned fmask[8];
+    if (threadIdx.x < N0)
+    {
+        r0[threadIdx.x] = op.dim[0].roots[threadIdx.x];
+        v0[threadIdx.x] = op.dim[0].den[N0 + threadIdx.x];
+    }
+    if (threadIdx.x < N1)
+    {
+        r1[threadIdx.x] = op.dim[1].roots[threadIdx.x];
+        v1[threadIdx.x] = op.dim[1].den[N1 + threadIdx.x];
+    }
+    if (threadIdx.x < 8)
+        fmask[threadIdx.x] = masks.m[threadIdx.x];
+    bool need_a = false, need_b = false, der0 = false;
+#pragma unroll
+    for (int f = 0; f < 8; ++f)
+        if (f < n_fields)
+        {
+            need_a |= !(masks.m[f] & 2u);
+            need_b |= (masks.m[f] & 2u) != 0;
+            der0 |= (masks.m[f] & 1u) != 0;
+        }
+    const size_t n_tiles = (E + TE - 1) / TE;
+    for (size_t t = blockIdx.x; t < n_tiles; t += gridDim.x)
+    {
+        const size_t e0 = t * TE;
+        const int ne = (int)((E - e0) < (size_t)TE ? (E - e0) : (size_t)TE);
+        const size_t items = (size_t)ne * P;
+        // the coordinates of this thread's first point are requested together with the DoF tile: one memory latency per
+        // tile instead of two
+        double px0 = 0.0, px1 = 0.0;
+        if (threadIdx.x < items)
+        {
+            const size_t el = threadIdx.x / P, p = threadIdx.x - el * P;
+            px0 = __ldcs(x + (e0 + el) * 2 * P + p);
+            px1 = __ldcs(x + (e0 + el) * 2 * P + P + p);
+        }
+        __syncthreads(); // DoFs of the previous tile consumed (and the root tables written)
+        for (int i = threadIdx.x; i < ne * N; i += blockDim.x)
+            c[i] = __ldcs(dofs + e0 * N + i);
+        __syncthreads();
+        for (size_t it = threadIdx.x; it < items; it += blockDim.x)
+        {
+            const int el = (int)(it / P);
+            const size_t p = it - (size_t)el * P;
+            const size_t e = e0 + el;
+            const double *xe = x + e * 2 * P;
+            const bool first = it == threadIdx.x;
+            const double x0 = first ? px0 : __ldcs(xe + p), x1 = first ? px1 : __ldcs(xe + P + p);
+            double t1v[N1], t1d[N1];
+            pt_lagrange_reg<N1>(r1, v1, x1, need_b, t1v, t1d);
+            const double *ce = c + el * N;
+            double sa[N0], sb[N0]; // sum_i1 c[i0][i1] * (value | derivative) of dimension 1
+#pragma unroll
+            for (int i0 = 0; i0 < N0; ++i0)
+            {
+                double a = 0.0, b = 0.0;
+#pragma unroll
+                for (int i1 = 0; i1 < N1; ++i1)
+                {
+                    const double cv = ce[i0 * N1 + i1];
+                    if (need_a)
+                        a = fma(cv, t1v[i1], a);
+                    if (need_b)
+                        b = fma(cv, t1d[i1], b);
+                }
+                sa[i0] = a, sb[i0] = b;
+            }
+            double t0v[N0], t0d[N0];
+            pt_lagrange_reg<N0>(r0, v0, x0, der0, t0v, t0d);
+            for (int f = 0; f < n_fields; ++f)
+            {
+                const unsigned m = fmask[f];
+                double acc = 0.0;
+#pragma unroll
+                for (int i0 = 0; i0 < N0; ++i0)
+                    acc = fma((m & 2u) ? sb[i0] : sa[i0], (m & 1u) ? t0d[i0] : t0v[i0], acc);
+                __stcs(out + (e * n_fields + f) * P + p, acc);
+            }
+        }
+    }
+}
+
+template <int N0, int N1>
+static void launch_points_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
+                                int n_fields, const PointMasks &pm, double *out)
+{
+    // elements per CTA pass: enough points to occupy every thread, at most 32 elements / 16 KB of DoFs
+    const int TE = (int)std::min<size_t>(32, std::max<size_t>(1, (kPtRegThreads + P - 1) / P));
+    const size_t smem = sizeof(double) * (2 * N0 + 2 * N1 + (size_t)TE * N0 * N1);
+    const size_t n_tiles = (E + TE - 1) / TE;
+    const int grid = (int)std::min<size_t>(n_tiles, (size_t)cfg.sm_count * 8);
+    points_reconstruct_reg2d_kernel<N0, N1><<<grid, kPtRegThreads, smem, cfg.stream>>>(op, TE, E, P, dofs, x, n_fields, pm, out);
+}
+
+// the instantiated shapes: n0, n1 <= 8 and |n0 - n1| <= 1 (isotropic spaces and the k-form component spaces p x (p+1))
+static bool dispatch_points_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
+                                  int n_fields, const PointMasks &pm, double *out)
+{
+#define IB_PT_CASE(A, B)                                                                                                        \
+    case (A) * 16 + (B):                                                                                                        \
+        launch_points_reg2d<A, B>(cfg, op, E, P, dofs, x, n_fields, pm, out);                                                    \
+        return true;
+#define IB_PT_ROW(A) IB_PT_CASE(A, A) IB_PT_CASE(A, A + 1) IB_PT_CASE(A + 1, A)
+    switch (op.dim[0].n * 16 + op.dim[1].n)
+    {
+        IB_PT_ROW(1) IB_PT_ROW(2) IB_PT_ROW(3) IB_PT_ROW(4) IB_PT_ROW(5) IB_PT_ROW(6) IB_PT_ROW(7) IB_PT_CASE(8, 8)
+    }
+#undef IB_PT_ROW
+#undef IB_PT_CASE
+    return false;
+}
+
 __global__ void __launch_bounds__(128)
     points_evaluate_coop_kernel(const PointOp op, int PB, size_t E, size_t P, const double *__restrict__ x, double *__restrict__ out)
 {
@@ -841,6 +997,16 @@ int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E,
     for (int k = 0; k < op.ndim; ++k)
         if (op.dim[k].n > PT_MAXN)
             return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
+    const auto has_roots = [](int type) { return type != BASIS_LEGENDRE && type != BASIS_BERNSTEIN; };
+    if (op.ndim == 2 && has_roots(op.dim[0].type) && has_roots(op.dim[1].type) && !getenv("IB200_POINTS_NO_REG") &&
+        dispatch_points_reg2d(cfg, op, E, P, dofs, x, (int)n_fields, pm, out))
+    {
+        ++*cfg.launch_counter;
+        const cudaError_t err = cudaGetLastError();
+        if (err != cudaSuccess)
+            return ib200_fail(IB200_ERROR_CUDA, "launch of points_reconstruct_reg2d_kernel failed: %s", cudaGetErrorString(err));
+        return INTERP_SUCCESS;
+    }
     int PB = 0;
     dim3 grid;
     const size_t smem = coop_shape(cfg, op, E, P, any_deriv, true, &PB, &grid);
