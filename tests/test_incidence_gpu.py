@@ -37,6 +37,25 @@ def test_dof_derivative_vs_oracle_bit_exact(ctx, orc, basis, E):
         assert np.array_equal(ctx.dof_derivative(basis, dofs, k), orc.dof_derivative(basis, dofs, k))
 
 
+@pytest.mark.parametrize("order", [1, 2, 6, 11, 12])
+@pytest.mark.parametrize("E", [1, 2, 63, 4097])
+def test_dof_derivative_kernel_variants_bit_identical(ctx, orc, order, E, monkeypatch):
+    """Orders up to 12 run the line-per-thread kernel with bulk-copied tiles (full tiles through cp.async.bulk, the
+    ragged tail through plain loads); IB200_DERIV_NO_COLS sends the same call to the tiled kernel.  Same bits, and the
+    oracle's, for every family and both dimensions."""
+    for bt in ("lagrange-gauss-lobatto", "legendre", "bernstein"):
+        basis = [(bt, order), ("lagrange-gauss", 3)]
+        N = (order + 1) * 4
+        dofs = np.random.default_rng(E + order).standard_normal((E, N))
+        for k in range(2):
+            got = ctx.dof_derivative(basis, dofs, k)
+            monkeypatch.setenv("IB200_DERIV_NO_COLS", "1")
+            tiled = ctx.dof_derivative(basis, dofs, k)
+            monkeypatch.delenv("IB200_DERIV_NO_COLS")
+            assert np.array_equal(got, tiled), (bt, k)
+            assert np.array_equal(got, orc.dof_derivative(basis, dofs, k)), (bt, k)
+
+
 @pytest.mark.parametrize("bt", ALL_BASIS)
 def test_derivative_is_incidence_matrix_times_dofs(ctx, bt):
     """tests/test_incidence.py:44-60: DegreesOfFreedom.derivative == incidence @ values (1-D), here for 2^16 elements."""

@@ -66,6 +66,29 @@ def test_points_vs_oracle(ctx, orc, basis, E, P):
         assert _err(ctx.evaluate_points(basis, x), orc.evaluate_points(basis, x)) < TOL
 
 
+@pytest.mark.parametrize("orders", [(6, 6), (1, 1), (3, 4), (5, 4), (7, 7), (0, 1)])
+@pytest.mark.parametrize("E,P", [(5, 64), (131, 50), (3, 300), (200, 1)])
+def test_points_register_kernel_is_bit_identical_to_the_cooperative_one(ctx, orc, orders, E, P, monkeypatch):
+    """2-D Lagrange-family spaces with n <= 8 run the thread-per-point register kernel (compile-time shapes); the same
+    call with IB200_POINTS_NO_REG goes through the cooperative shared-memory kernel: identical bits, every field mask,
+    ragged tiles (E not a multiple of the elements per pass, P not a multiple of the warp) -- and both within TOL of
+    the oracle."""
+    basis = [("lagrange-gauss-lobatto", orders[0]), ("lagrange-gauss", orders[1])]
+    rng = np.random.default_rng(E * 77 + P)
+    N = (orders[0] + 1) * (orders[1] + 1)
+    x = rng.uniform(-1, 1, (E, 2, P))
+    dofs = rng.standard_normal((E, N))
+    for masks in ([0], [0, 1, 2], [3, 2, 1, 0, 1], [1], [2, 2]):
+        got = ctx.reconstruct_points(basis, dofs, x, masks)
+        monkeypatch.setenv("IB200_POINTS_NO_REG", "1")
+        coop = ctx.reconstruct_points(basis, dofs, x, masks)
+        monkeypatch.delenv("IB200_POINTS_NO_REG")
+        assert np.array_equal(got, coop), f"masks {masks}"
+        ref = orc.reconstruct_points(basis, dofs, x, masks)
+        for f in range(len(masks)):
+            assert _err(got[:, f], ref[:, f]) < TOL, f"masks {masks} field {f}"
+
+
 def test_points_empty_and_bad_arguments(ctx):
     basis = [("lagrange-gauss-lobatto", 2)] * 2
     assert ctx.reconstruct_points(basis, np.zeros((0, 9)), np.zeros((0, 2, 5))).shape == (0, 1, 5)
