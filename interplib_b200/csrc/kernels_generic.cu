@@ -664,6 +664,211 @@ static void launch_spd_solve_reg(const LaunchCfg &cfg, size_t E, const double *m
     spd_solve_reg_kernel<N><<<(int)blocks, 128, smem, cfg.stream>>>(E, mass, rhs);
 }
 
+// Blocked variant for n > 32: ONE CTA PER ELEMENT, right-looking Cholesky in 32-column block steps on the matrix extended
+// by the right-hand side as row n (so the forward substitution is the same recurrence as the panel solve):
+//   1. the 32 x 32 diagonal block goes to shared memory and is factorised by warp 0 in registers (lane = row, as in
+//      spd_solve_reg_kernel; a ragged last block is padded with the identity);
+//   2. panel: one thread per row below the block solves x L_kk^T = a (32 entries in registers, L_kk rows as broadcasts),
+//      writes x back into the matrix (the factor) and, transposed, into the shared-memory panel PT[m][row];
+//   3. trailing update A[i][j] -= sum_m P[i][m] P[j][m] on 4 x 4 tiles of the lower triangle, two LDS.128 per operand and m.
+// Then L^T u = y in 32-row blocks from the bottom: warp 0 solves the diagonal block with shuffles, every thread i above
+// it subtracts its 32 products (factor rows read with unit stride across threads).
+// The matrix is staged in shared memory when it fits (n <= 127: read once, left untouched); larger systems are factorised
+// in place in device memory (they stay L2 resident: 0.67 MB per CTA at n = 289), as the C-ABI contract says.
+constexpr int kCholNB = 32, kCholLD = 33;
+
+__device__ __forceinline__ void chol_diag32(double *D, double *rinv_out, int lane)
+{
+    // D[32][33] (lower triangle valid, padded with the identity) -> L in place (row major), 1 / L[k][k] to rinv_out[k]
+    double a[kCholNB];
+#pragma unroll
+    for (int j = 0; j < kCholNB; ++j)
+        a[j] = D[lane * kCholLD + j];
+    __syncwarp();
+    double rinv = 0.0;
+#pragma unroll
+    for (int k = 0; k < kCholNB; ++k)
+    {
+        const double r = rsqrt(__shfl_sync(0xffffffffu, a[k], k));
+        a[k] *= r;
+        if (lane == k)
+            rinv = r;
+        if (k + 1 < kCholNB)
+        {
+            D[lane * kCholLD + k] = a[k]; // column k of L (rows < k keep scaled garbage of the upper triangle: never read)
+            __syncwarp();
+#pragma unroll
+            for (int j = k + 1; j < kCholNB; ++j)
+                a[j] = fma(-a[k], D[j * kCholLD + k], a[j]);
+        }
+        else
+            D[lane * kCholLD + k] = a[k];
+    }
+    rinv_out[lane] = rinv;
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(256)
+    spd_solve_blocked_kernel(int n, int lda, bool staged, size_t E, double *__restrict__ mass, double *__restrict__ rhs)
+{
+    extern __shared__ __align__(16) double chol_blk_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, nthr = blockDim.x;
+    const int RP = (n + 1 + 3) & ~3; // panel row capacity (rows below the first block + the right-hand side), 4-aligned
+    double *D = chol_blk_smem;                    // [32][33]
+    double *PT = chol_blk_smem + ((kCholNB * kCholLD + 1) & ~1); // [32][RP] transposed panel, 16-byte aligned
+    double *rinv = PT + kCholNB * RP;             // [n + 32]
+    double *y = rinv + ((n + kCholNB + 1) & ~1);  // [n + 32]
+    double *As = y + ((n + kCholNB + 1) & ~1);    // [(n + 1)][lda] when staged
+    for (size_t e = blockIdx.x; e < E; e += gridDim.x)
+    {
+        double *Ag = mass + e * (size_t)n * n;
+        double *bg = rhs + e * (size_t)n;
+        double *A = staged ? As : Ag;
+        double *brow = staged ? As + (size_t)n * lda : bg; // row n of the extended matrix
+        __syncthreads();
+        if (staged)
+        {
+            for (int idx = tid, i = 0, j = tid; idx < n * n; idx += nthr, j += nthr)
+            {
+                while (j >= n)
+                    j -= n, ++i;
+                As[i * lda + j] = __ldcs(Ag + idx);
+            }
+            for (int j = tid; j < n; j += nthr)
+                brow[j] = bg[j];
+        }
+        __syncthreads();
+        for (int kb = 0; kb < n; kb += kCholNB)
+        {
+            const int nb = n - kb < kCholNB ? n - kb : kCholNB;
+            const int k1 = kb + nb;      // first trailing row / column
+            const int R = n + 1 - k1;    // rows below the block, the right-hand side included
+            // 1. diagonal block (identity padding for a ragged block)
+            for (int idx = tid; idx < kCholNB * kCholNB; idx += nthr)
+            {
+                const int i = idx >> 5, j = idx & 31;
+                D[i * kCholLD + j] = (i < nb && j < nb) ? A[(size_t)(kb + i) * lda + kb + j] : (i == j ? 1.0 : 0.0);
+            }
+            __syncthreads();
+            if (tid < 32)
+                chol_diag32(D, rinv + kb, lane);
+            __syncthreads();
+            // the factor's diagonal block back into the matrix (the back substitution reads it there)
+            for (int idx = tid; idx < nb * nb; idx += nthr)
+            {
+                const int i = idx / nb, j = idx - i * nb;
+                if (j <= i)
+                    A[(size_t)(kb + i) * lda + kb + j] = D[i * kCholLD + j];
+            }
+            // 2. panel rows k1 .. n (row n = right-hand side)
+            for (int r = tid; r < R; r += nthr)
+            {
+                const int i = k1 + r;
+                double *row = (i < n ? A + (size_t)i * lda : brow) + kb;
+                double xv[kCholNB];
+#pragma unroll
+                for (int j = 0; j < kCholNB; ++j)
+                    xv[j] = j < nb ? row[j] : 0.0;
+#pragma unroll
+                for (int j = 0; j < kCholNB; ++j)
+                {
+                    double sacc = xv[j];
+#pragma unroll
+                    for (int m = 0; m < j; ++m)
+                        sacc = fma(-xv[m], D[j * kCholLD + m], sacc);
+                    xv[j] = sacc * rinv[kb + j];
+                }
+#pragma unroll
+                for (int j = 0; j < kCholNB; ++j)
+                {
+                    if (j < nb)
+                        row[j] = xv[j];
+                    PT[j * RP + r] = xv[j];
+                }
+            }
+            __syncthreads();
+            // 3. trailing update on 4 x 4 tiles (ti >= tj) of rows/columns k1 ..; row n is the right-hand side
+            const int nt = (R + 3) >> 2;
+            const int n_tiles = nt * (nt + 1) / 2;
+            for (int t = tid; t < n_tiles; t += nthr)
+            {
+                int ti = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+                while ((ti + 1) * (ti + 2) / 2 <= t)
+                    ++ti;
+                while (ti * (ti + 1) / 2 > t)
+                    --ti;
+                const int tj = t - ti * (ti + 1) / 2;
+                double acc[4][4] = {};
+                const double *pi = PT + 4 * ti, *pj = PT + 4 * tj;
+#pragma unroll 8
+                for (int m = 0; m < kCholNB; ++m)
+                {
+                    const double2 a01 = *reinterpret_cast<const double2 *>(pi + m * RP);
+                    const double2 a23 = *reinterpret_cast<const double2 *>(pi + m * RP + 2);
+                    const double2 b01 = *reinterpret_cast<const double2 *>(pj + m * RP);
+                    const double2 b23 = *reinterpret_cast<const double2 *>(pj + m * RP + 2);
+                    const double av[4] = {a01.x, a01.y, a23.x, a23.y}, bv[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+                    for (int a = 0; a < 4; ++a)
+#pragma unroll
+                        for (int b = 0; b < 4; ++b)
+                            acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+                }
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+                {
+                    const int i = k1 + 4 * ti + a;
+                    if (i > n)
+                        continue;
+                    double *row = i < n ? A + (size_t)i * lda : brow;
+#pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                    {
+                        const int j = k1 + 4 * tj + b;
+                        if (j < n && j <= i)
+                            row[j] -= acc[a][b];
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        // y = L^-1 b sits in row n;  L^T u = y from the bottom block up
+        for (int j = tid; j < n; j += nthr)
+            y[j] = brow[j];
+        __syncthreads();
+        for (int kb = ((n - 1) / kCholNB) * kCholNB; kb >= 0; kb -= kCholNB)
+        {
+            const int nb = n - kb < kCholNB ? n - kb : kCholNB;
+            if (tid < 32)
+            {
+                double yv = lane < nb ? y[kb + lane] : 0.0;
+                const double ri = lane < nb ? rinv[kb + lane] : 0.0;
+                for (int k = nb - 1; k >= 0; --k)
+                {
+                    const double uk = __shfl_sync(0xffffffffu, yv * ri, k);
+                    if (lane == k)
+                        yv = uk;
+                    else if (lane < k)
+                        yv = fma(-A[(size_t)(kb + k) * lda + kb + lane], uk, yv);
+                }
+                if (lane < nb)
+                    y[kb + lane] = yv;
+            }
+            __syncthreads();
+            for (int i = tid; i < kb; i += nthr)
+            {
+                double yv = y[i];
+                for (int k = 0; k < nb; ++k)
+                    yv = fma(-A[(size_t)(kb + k) * lda + i], y[kb + k], yv);
+                y[i] = yv;
+            }
+            __syncthreads();
+        }
+        for (int j = tid; j < n; j += nthr)
+            bg[j] = y[j];
+    }
+}
+
 // ---- projection norms: deterministic two-pass dot product sum_i a[i]*b[i] (fixed block -> partial mapping) ----
 constexpr int kDotBlocks = 592; // 4 CTAs per SM on 148 SMs
 
@@ -799,6 +1004,22 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
 #undef IB_SPD_CASE
         ++*cfg.launch_counter;
         return check_launch("spd_solve_reg_kernel");
+    }
+    if (!getenv("IB200_SPD_NO_BLOCKED"))
+    {
+        const bool staged = n <= 127;
+        const int lda = staged ? ((int)n | 1) : (int)n;
+        const int RP = ((int)n + 1 + 3) & ~3, vec = ((int)n + kCholNB + 1) & ~1;
+        const size_t smem = sizeof(double) * (((kCholNB * kCholLD + 1) & ~1) + (size_t)kCholNB * RP + 2 * vec +
+                                              (staged ? (size_t)(n + 1) * lda : 0));
+        const int threads = n <= 64 ? 128 : 256;
+        IB_CUDA(cudaFuncSetAttribute(spd_solve_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        int per_sm = 0;
+        IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_blocked_kernel, threads, smem));
+        const size_t grid = std::min<size_t>(E, (size_t)cfg.sm_count * std::max(per_sm, 1));
+        spd_solve_blocked_kernel<<<(int)grid, threads, smem, cfg.stream>>>((int)n, lda, staged, E, mass, rhs);
+        ++*cfg.launch_counter;
+        return check_launch("spd_solve_blocked_kernel");
     }
     const size_t warps = E;
     size_t blocks = (warps * 32 + 127) / 128;

@@ -60,6 +60,19 @@ def main():
     report("N1 spd_solve 25x25 (read M + b, write u)", E, 8 * (cfg.N * cfg.N + 2 * cfg.N), ms)
     for b in (d_g, d_f, d_M, d_b):
         b.free()
+    # ---- N1 at the C2 (49 x 49, shared-memory kernel) and C4 (289 x 289, in-place kernel) system sizes: random SPD matrices
+    for n, E in ((49, 1 << 16), (289, 1 << 10)):
+        G = rng.standard_normal((E, n, n))
+        M = G @ np.swapaxes(G, 1, 2) + n * np.eye(n)
+        b = rng.standard_normal((E, n))
+        d_M, d_b = ctx.alloc(M.nbytes).upload(M), ctx.alloc(b.nbytes).upload(b)
+        del G
+        # the in-place kernel (n > 127) overwrites M with its factor: upload it again before every timed call
+        restore = (lambda d_M=d_M, M=M: d_M.upload(M)) if n > 127 else None
+        ms = timed(ctx, lambda: ctx.spd_solve(d_M.ptr, d_b.ptr, where=DEVICE, n=n, n_elements=E), setup=restore)
+        report(f"N1 spd_solve {n}x{n} (read M + b, write u)", E, 8 * (n * n + 2 * n), ms)
+        for buf in (d_M, d_b):
+            buf.free()
     # ---- N2: reconstruct value + gradient at 64 arbitrary points per element, C2 space, 2^18 elements
     cfg = syn.CONFIGS["c2"]
     basis = list(cfg.basis)
