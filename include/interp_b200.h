@@ -323,6 +323,15 @@ IB200_API int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, cons
 IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
                                     int where);
 
+/* The whole projection_l2_primal of a batch in one call (python/interplib/integration.py:171-223: dual projection, mass
+ * matrix, np.linalg.solve): geometry + f samples in, primal[E][N] out.  The mass matrices are assembled into the context's
+ * scratch, solved there (Cholesky) and never leave the device: a HOST call moves 8(n_phys*N_geom + Q) bytes in and 8 N
+ * bytes out per element instead of the 8 N^2 of ib200_l2_system_mapped_batch. */
+IB200_API int ib200_l2_project_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                            const integration_spec_t *rules, unsigned n_phys,
+                                            const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                            const double *fvals, double *primal, int where);
+
 /* ---- 8(e): projection norms -------------------------------------------------------------------- */
 /* out[0] = sum_i a[i]*b[i] in FP64 with a fixed (deterministic) reduction tree.  The per-rank partial of the
  * norms a partitioned projection reports -- sum_e b_e.u_e (= ||Pi f||^2), sum_e sum_q f^2 W det (= ||f||^2, with

@@ -167,6 +167,11 @@ _PROTOTYPES = {
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
     ),
+    "ib200_l2_project_mapped_batch": (
+        C.c_int,
+        [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
+         C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
+    ),
     "ib200_spd_solve_batch": (C.c_int, [C.c_void_p, C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]),
     "ib200_dot": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
 }

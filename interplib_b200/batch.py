@@ -319,6 +319,22 @@ class Context:
         return mass, rhs
 
     # -- N1 ----------------------------------------------------------------------------------------
+    def l2_project_mapped(self, basis, rules, geom_basis, geom_dofs, n_phys, fvals, out=None, where=HOST, n_elements=None):
+        """projection_l2_primal of a whole batch: geometry + f samples -> primal DoFs u[E][N]; the mass matrices stay in
+        device scratch   (ib200_l2_project_mapped_batch)"""
+        N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if where == HOST:
+            fvals = _as_in(fvals, (-1, Q))
+            E = fvals.shape[0]
+            geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
+            if out is None:
+                out = np.empty((E, N))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_l2_project_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
+                                                basis_specs(geom_basis), E, _ptr(geom_dofs), _ptr(fvals), _ptr(out), where))
+        return out
+
     def spd_solve(self, mass, rhs, where=HOST, n=None, n_elements=None):
         """Solve mass[e] u = rhs[e] for every element (Cholesky on the GPU); returns u[E][N]."""
         if where == HOST:

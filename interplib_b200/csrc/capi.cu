@@ -1230,17 +1230,18 @@ extern "C" int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const
 }
 
 // ---- K2 + K3 fused ------------------------------------------------------------------------------------------
-extern "C" int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
-                                            const integration_spec_t *rules, unsigned n_phys,
-                                            const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
-                                            const double *fvals, double *mass, double *rhs, int where)
+// (M, b) per element, and with `solve` the primal DoFs u = M^-1 b: M then lives in the context's scratch only (mass ==
+// NULL) and `rhs` receives u
+static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, const integration_spec_t *rules,
+                          unsigned n_phys, const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                          const double *fvals, double *mass, double *rhs, int where, bool solve)
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
     IB_TRY(check_geometry_dims(ndim, n_phys));
     if (!basis || !geom_basis)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/geom_basis must not be NULL");
-    if (n_elements && (!fvals || !mass || !rhs || !geom_dofs))
+    if (n_elements && (!fvals || (!mass && !solve) || !rhs || !geom_dofs))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/fvals/mass/rhs must not be NULL");
     OpDesc op, gop;
     OpHost host, ghost;
@@ -1253,15 +1254,10 @@ extern "C" int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, con
     const std::string key_l2w = plan_key("l2", ndim, basis, nullptr, rules, nullptr, 1, 0, 0, 0);
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
                                       {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
-                                      {ARR_OUT, mass, sizeof(double) * op.N_out * op.N_in},
+                                      {solve ? ARR_SCRATCH : ARR_OUT, solve ? nullptr : mass, sizeof(double) * op.N_out * op.N_in},
                                       {ARR_OUT, rhs, sizeof(double) * op.N_in},
                                       {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
-    return run_batched(ctx, n_elements, arrays, where, 0,
-                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
-                           const double *g = (const double *)dev[0], *f = (const double *)dev[1];
-                           double *M = (double *)dev[2], *b = (double *)dev[3], *w = (double *)dev[4];
-                           if (!cnt)
-                               return INTERP_SUCCESS;
+    const auto assemble = [&](const LaunchCfg &cfg, size_t cnt, const double *g, const double *f, double *M, double *b, double *w) -> int {
                            if (!cfg.force_generic && fuse_geometry)
                            {
                                if (ctx->lo_kernel)
@@ -1291,7 +1287,30 @@ extern "C" int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, con
                            if (res == IB200_ERROR_UNSUPPORTED)
                                res = launch_l2_generic(cfg, op, cnt, f, w, b);
                            return res;
-                       });
+    };
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        if (!cnt)
+            return INTERP_SUCCESS;
+        double *M = (double *)dev[2], *b = (double *)dev[3];
+        IB_TRY(assemble(cfg, cnt, (const double *)dev[0], (const double *)dev[1], M, b, (double *)dev[4]));
+        return solve ? launch_spd_solve(cfg, op.N_in, cnt, M, b) : INTERP_SUCCESS;
+    });
+}
+
+extern "C" int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                            const integration_spec_t *rules, unsigned n_phys,
+                                            const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                            const double *fvals, double *mass, double *rhs, int where)
+{
+    return l2_system_impl(ctx, ndim, basis, rules, n_phys, geom_basis, n_elements, geom_dofs, fvals, mass, rhs, where, false);
+}
+
+extern "C" int ib200_l2_project_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
+                                             const integration_spec_t *rules, unsigned n_phys,
+                                             const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                             const double *fvals, double *primal, int where)
+{
+    return l2_system_impl(ctx, ndim, basis, rules, n_phys, geom_basis, n_elements, geom_dofs, fvals, nullptr, primal, where, true);
 }
 
 // ---- N1 ----------------------------------------------------------------------------------------------------

@@ -60,6 +60,34 @@ def main():
     report("N1 spd_solve 25x25 (read M + b, write u)", E, 8 * (cfg.N * cfg.N + 2 * cfg.N), ms)
     for b in (d_g, d_f, d_M, d_b):
         b.free()
+    # ---- N1 fused: the whole projection_l2_primal of C5 (geometry + f -> u; M assembled and solved in device scratch)
+    E = 1 << 20
+    geom = syn.geometry(cfg, first=0, count=E)
+    f = rng.standard_normal((E, cfg.Q))
+    d_g, d_f, d_u = ctx.alloc(geom.nbytes).upload(geom), ctx.alloc(f.nbytes).upload(f), ctx.alloc(E * cfg.N * 8)
+    ms = timed(ctx, lambda: ctx.l2_project_mapped(basis, rules, gb, d_g.ptr, 2, d_f.ptr, out=d_u.ptr, where=DEVICE, n_elements=E))
+    report("N1 l2_project C5 (geometry + f -> u), device resident", E, 8 * (geom.shape[1] * geom.shape[2] + cfg.Q + cfg.N), ms)
+    for buf in (d_g, d_f, d_u):
+        buf.free()
+    import time
+
+    u = np.empty((E, cfg.N))
+    best = 1e30
+    for _ in range(4):
+        t0 = time.perf_counter()
+        ctx.l2_project_mapped(basis, rules, gb, geom, 2, f, out=u)
+        best = min(best, time.perf_counter() - t0)
+    print(json.dumps({"kernel": "N1 l2_project C5 end to end (host arrays through the C-ABI)", "elements": E, "ms": round(best * 1e3, 3),
+                      "elements_per_s": E / best, "h2d_bytes": geom.nbytes + f.nbytes, "d2h_bytes": u.nbytes}))
+    best = 1e30
+    for _ in range(2):
+        t0 = time.perf_counter()
+        M, b = ctx.l2_system_mapped(basis, rules, gb, geom, 2, f)
+        ctx.spd_solve(M, b)
+        best = min(best, time.perf_counter() - t0)
+    print(json.dumps({"kernel": "N1 same projection as l2_system + spd_solve with M through the host (r01e flow)", "elements": E,
+                      "ms": round(best * 1e3, 3), "elements_per_s": E / best}))
+    del M, b, u, geom, f
     # ---- N1 at the C2 (49 x 49, shared-memory kernel) and C4 (289 x 289, in-place kernel) system sizes: random SPD matrices
     for n, E in ((49, 1 << 16), (289, 1 << 10)):
         G = rng.standard_normal((E, n, n))
