@@ -2,7 +2,9 @@
 // cache, host<->device staging for host-pointer calls, and dispatch to the CUDA kernels.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 #include <string>
+#include <thread>
 
 #include "ctx.cuh"
 
@@ -589,6 +591,31 @@ struct BatchArray
     size_t elem_bytes; // bytes per element
 };
 
+// Copies between a caller's pageable array and a pinned staging slot: one host thread moves about 10 GB/s, a fifth of what
+// PCIe then carries, so slabs of 2 MB and more are split over a few threads (IB200_STAGE_THREADS, default 4, 1 = off).
+void stage_memcpy(void *dst, const void *src, size_t bytes)
+{
+    static const int n_threads = [] {
+        const char *env = getenv("IB200_STAGE_THREADS");
+        const int want = env ? atoi(env) : 4;
+        const int hw = (int)std::thread::hardware_concurrency();
+        return std::max(1, std::min(want, hw > 1 ? hw / 2 : 1));
+    }();
+    if (n_threads == 1 || bytes < ((size_t)2 << 20))
+    {
+        std::memcpy(dst, src, bytes);
+        return;
+    }
+    const size_t part = ((bytes / n_threads) + 4095) & ~(size_t)4095;
+    std::thread workers[16];
+    int n = 0;
+    for (size_t off = part; off < bytes && n < 15; off += part, ++n)
+        workers[n] = std::thread([=] { std::memcpy((char *)dst + off, (const char *)src + off, std::min(part, bytes - off)); });
+    std::memcpy(dst, src, std::min(part, bytes));
+    for (int i = 0; i < n; ++i)
+        workers[i].join();
+}
+
 bool host_pointer_is_pinned(const void *p)
 {
     cudaPointerAttributes attr;
@@ -701,10 +728,14 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
         return INTERP_SUCCESS;
 
     // ---- host pointers: three slots, each with its own stream, device slab and pinned slab -----------------
-    size_t per_elem = 0;
+    size_t per_elem = 0, dev_per_elem = 0; // bytes that cross PCIe / bytes of the device slab (scratch included)
     for (auto &a : arrays)
-        if (a.ptr || a.kind == ARR_SCRATCH)
+    {
+        if (a.ptr)
             per_elem += a.elem_bytes;
+        if (a.ptr || a.kind == ARR_SCRATCH)
+            dev_per_elem += a.elem_bytes;
+    }
     size_t chunk = ctx->chunk_elements;
     if (chunk == 0)
     {
@@ -712,7 +743,8 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
         // every chunk starts on a 4 KB boundary of the host arrays (measured on C2: 48 MB chunks of an odd element count
         // 32.8 ms per 2^20 elements, 16 MB chunks of 8192 elements 30.4 ms = 53 GB/s device-to-host)
         const size_t target = (size_t)16 << 20;
-        const size_t fit = target / std::max<size_t>(per_elem, 1);
+        // scratch never crosses PCIe: it only bounds the chunk through the device slab (256 MB per slot)
+        const size_t fit = std::min(target / std::max<size_t>(per_elem, 1), ((size_t)256 << 20) / std::max<size_t>(dev_per_elem, 1));
         chunk = fit >= 512 ? (fit & ~(size_t)511) : std::max<size_t>(256, fit); // big elements: launches of >= 256
     }
     chunk = std::min(chunk, E);
@@ -752,8 +784,8 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
             const BatchArray &a = arrays[i];
             if (!a.ptr || pinned[i] || (a.kind != ARR_OUT && a.kind != ARR_INOUT))
                 continue;
-            std::memcpy((char *)a.ptr + pending[s].first * a.elem_bytes, (char *)ctx->stage_pin[s] + pin_off[i],
-                        pending[s].cnt * a.elem_bytes);
+            stage_memcpy((char *)a.ptr + pending[s].first * a.elem_bytes, (char *)ctx->stage_pin[s] + pin_off[i],
+                         pending[s].cnt * a.elem_bytes);
         }
         pending[s].busy = false;
         return INTERP_SUCCESS;
@@ -775,7 +807,7 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
             const char *src = (const char *)a.ptr + first * a.elem_bytes;
             if (!pinned[i])
             {
-                std::memcpy((char *)ctx->stage_pin[slot] + pin_off[i], src, cnt * a.elem_bytes);
+                stage_memcpy((char *)ctx->stage_pin[slot] + pin_off[i], src, cnt * a.elem_bytes);
                 src = (const char *)ctx->stage_pin[slot] + pin_off[i];
             }
             IB_CUDA(cudaMemcpyAsync(dev[i], src, cnt * a.elem_bytes, cudaMemcpyHostToDevice, st));
