@@ -664,6 +664,145 @@ static void launch_spd_solve_reg(const LaunchCfg &cfg, size_t E, const double *m
     spd_solve_reg_kernel<N><<<(int)blocks, 128, smem, cfg.stream>>>(E, mass, rhs);
 }
 
+// Two-block register variant for 33 <= n <= 64 (the C2 space is 49 x 49, a C3 block pair 72 is beyond it): still ONE WARP
+// PER ELEMENT and no CTA barrier.  Rows 0..31 are factorised as in spd_solve_reg_kernel (lane = row, columns of L11 to
+// shared memory); then lane r takes row 32 + r: its 32 entries of A21 are solved against L11 in registers (x L11^T = a,
+// L11 as warp-uniform broadcasts) and stored as panel row X[r]; its row of the Schur complement A22 - X X^T is formed
+// in registers (X rows as broadcasts, two per LDS.128) and factorised by the same routine, padded with the identity to
+// 32 x 32.  The right-hand side rides along in two registers (y1, y2); the back substitution runs block 2, then
+// y1 -= X^T u2, then block 1.  Rows come straight from global memory (a lane reads its own row: every sector is used by
+// four consecutive loads and stays in L1).
+constexpr int kReg2LD = 33, kReg2XLD = 34;
+
+// a[32]: row `lane` of a 32 x 32 SPD block (lower triangle valid) -> L in place, columns to S[k][i] = l_ik; forward
+// substitution of y on the way; returns 1 / l_lane,lane
+__device__ __forceinline__ double chol_factor32(double (&a)[32], double &y, double *S, int lane, int n_act)
+{
+    double rinv = 0.0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k)
+    {
+        if (k >= n_act) // warp uniform: the identity padding needs no work (y = 0 there)
+            break;
+        const double r = rsqrt(__shfl_sync(0xffffffffu, a[k], k));
+        a[k] *= r;
+        const double yk = __shfl_sync(0xffffffffu, y, k) * r;
+        if (lane == k)
+            y = yk, rinv = r;
+        else if (lane > k)
+            y = fma(-a[k], yk, y);
+        S[k * kReg2LD + lane] = a[k];
+        if (k + 1 < 32)
+        {
+            __syncwarp();
+#pragma unroll
+            for (int j = k + 1; j < 32; ++j)
+                a[j] = fma(-a[k], S[k * kReg2LD + j], a[j]);
+        }
+    }
+    __syncwarp();
+    return rinv;
+}
+
+// L^T u = y for a factor stored by chol_factor32 (l_ki = S[i][k]); y -> u in place
+__device__ __forceinline__ void chol_back32(double &y, double rinv, const double *S, int lane, int n_act)
+{
+#pragma unroll
+    for (int k = 31; k >= 0; --k)
+    {
+        if (k >= n_act)
+            continue;
+        const double uk = __shfl_sync(0xffffffffu, y * rinv, k);
+        if (lane == k)
+            y = uk;
+        else if (lane < k)
+            y = fma(-S[lane * kReg2LD + k], uk, y);
+    }
+}
+
+__global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, const double *__restrict__ mass, double *__restrict__ rhs)
+{
+    extern __shared__ __align__(16) double chol_reg2_smem[];
+    constexpr int PER_WARP = 2 * 32 * kReg2LD + 32 * kReg2XLD + 32; // S1 | S2 | X | y1
+    const int lane = threadIdx.x & 31;
+    double *S1 = chol_reg2_smem + (size_t)(threadIdx.x >> 5) * PER_WARP;
+    double *S2 = S1 + 32 * kReg2LD;
+    double *X = S2 + 32 * kReg2LD; // 16-byte aligned: 2 * 32 * 33 doubles and PER_WARP are even
+    double *Y1 = X + 32 * kReg2XLD;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    const int n2 = n - 32;
+    const bool valid = lane < n2;
+    const int rr = valid ? 32 + lane : 32; // idle lanes shadow row 32 for the panel (results never used)
+    for (size_t e = warp; e < E; e += n_warps)
+    {
+        const double *A = mass + e * (size_t)n * n;
+        double *b = rhs + e * (size_t)n;
+        __syncwarp();
+        double a[32], x[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            a[j] = A[(size_t)lane * n + j];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            x[j] = A[(size_t)rr * n + j];
+        double y1 = b[lane], y2 = valid ? b[32 + lane] : 0.0;
+        const double rinv1 = chol_factor32(a, y1, S1, lane, 32);
+        Y1[lane] = y1;
+        __syncwarp();
+        // panel: x L11^T = a21 (l_jm = S1[m][j]), and the forward substitution of y2 through it
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+        {
+            double sacc = x[j];
+#pragma unroll
+            for (int m = 0; m < j; ++m)
+                sacc = fma(-x[m], S1[m * kReg2LD + j], sacc);
+            x[j] = sacc * __shfl_sync(0xffffffffu, rinv1, j);
+            y2 = fma(-x[j], Y1[j], y2);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            X[lane * kReg2XLD + j] = x[j];
+        __syncwarp();
+        // Schur complement row: a22[j] - sum_m x[m] X[j][m] for the columns j < n2, identity beyond (and on idle lanes)
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+        {
+            double sacc = (j == lane) ? 1.0 : 0.0;
+            if (j < n2) // warp uniform
+            {
+                sacc = valid ? A[(size_t)rr * n + 32 + j] : sacc;
+                const double *xj = X + j * kReg2XLD;
+                double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+                for (int m = 0; m < 32; m += 2)
+                {
+                    const double2 v = *reinterpret_cast<const double2 *>(xj + m);
+                    s0 = fma(x[m], v.x, s0);
+                    s1 = fma(x[m + 1], v.y, s1);
+                }
+                if (valid)
+                    sacc -= s0 + s1;
+            }
+            a[j] = sacc;
+        }
+        if (!valid)
+            y2 = 0.0;
+        const double rinv2 = chol_factor32(a, y2, S2, lane, n2);
+        // back substitution: block 2, y1 -= X^T u2, block 1
+        chol_back32(y2, rinv2, S2, lane, n2);
+#pragma unroll
+        for (int r = 0; r < 32; ++r)
+            if (r < n2) // warp uniform
+                y1 = fma(-X[r * kReg2XLD + lane], __shfl_sync(0xffffffffu, y2, r), y1);
+        chol_back32(y1, rinv1, S1, lane, 32);
+        b[lane] = y1;
+        if (valid)
+            b[32 + lane] = y2;
+    }
+}
+
 // Blocked variant for n > 32: ONE CTA PER ELEMENT, right-looking Cholesky in 32-column block steps on the matrix extended
 // by the right-hand side as row n (so the forward substitution is the same recurrence as the panel solve):
 //   1. the 32 x 32 diagonal block goes to shared memory and is factorised by warp 0 in registers (lane = row, as in
@@ -1004,6 +1143,17 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
 #undef IB_SPD_CASE
         ++*cfg.launch_counter;
         return check_launch("spd_solve_reg_kernel");
+    }
+    if (n > 32 && n <= 64 && !getenv("IB200_SPD_NO_REG2"))
+    {
+        const int smem = (int)sizeof(double) * 4 * (2 * 32 * kReg2LD + 32 * kReg2XLD + 32);
+        IB_CUDA(cudaFuncSetAttribute(spd_solve_reg2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        int per_sm = 0;
+        IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_reg2_kernel, 128, smem));
+        const size_t blocks = std::min<size_t>((E + 3) / 4, (size_t)cfg.sm_count * std::max(per_sm, 1));
+        spd_solve_reg2_kernel<<<(int)blocks, 128, smem, cfg.stream>>>((int)n, E, mass, rhs);
+        ++*cfg.launch_counter;
+        return check_launch("spd_solve_reg2_kernel");
     }
     if (!getenv("IB200_SPD_NO_BLOCKED"))
     {
