@@ -526,6 +526,71 @@ static void launch_points_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t 
     points_reconstruct_reg2d_kernel<N0, N1><<<grid, kPtRegThreads, smem, cfg.stream>>>(op, TE, E, P, dofs, x, n_fields, pm, out);
 }
 
+// FunctionSpace.evaluate for the same spaces: a warp takes 32 consecutive points of one element, every lane builds the
+// 1-D values of its point in registers and writes the N products into the warp's shared-memory tile (odd row stride:
+// conflict free); the tile -- 32 N contiguous doubles of the output -- then leaves with coalesced streaming stores.
+// Same products as the cooperative kernel (1 * t0 * t1), bit-identical.
+template <int N0, int N1>
+__global__ void __launch_bounds__(kPtRegThreads)
+    points_evaluate_reg2d_kernel(const PointOp op, size_t E, size_t P, const double *__restrict__ x, double *__restrict__ out)
+{
+    extern __shared__ __align__(16) double pt_smem[];
+    constexpr int N = N0 * N1, NP = N | 1;
+    double *r0 = pt_smem, *v0 = r0 + N0, *r1 = v0 + N0, *v1 = r1 + N1;
+    const int lane = threadIdx.x & 31;
+    double *tile = v1 + N1 + (size_t)(threadIdx.x >> 5) * 32 * NP; // [32][NP] per warp
+    if (threadIdx.x < N0)
+    {
+        r0[threadIdx.x] = op.dim[0].roots[threadIdx.x];
+        v0[threadIdx.x] = op.dim[0].den[N0 + threadIdx.x];
+    }
+    if (threadIdx.x < N1)
+    {
+        r1[threadIdx.x] = op.dim[1].roots[threadIdx.x];
+        v1[threadIdx.x] = op.dim[1].den[N1 + threadIdx.x];
+    }
+    __syncthreads();
+    const size_t groups = (P + 31) / 32, total = E * groups;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+    const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t it = warp; it < total; it += n_warps)
+    {
+        const size_t e = it / groups, p0 = (it - e * groups) * 32;
+        const int np = (int)((P - p0) < 32 ? (P - p0) : 32);
+        const double *xe = x + e * 2 * P + p0;
+        const double x0 = lane < np ? __ldcs(xe + lane) : 0.0, x1 = lane < np ? __ldcs(xe + P + lane) : 0.0;
+        double t0v[N0], t0d[N0], t1v[N1], t1d[N1];
+        pt_lagrange_reg<N0>(r0, v0, x0, false, t0v, t0d);
+        pt_lagrange_reg<N1>(r1, v1, x1, false, t1v, t1d);
+        __syncwarp(); // the previous tile has been copied out
+#pragma unroll
+        for (int i0 = 0; i0 < N0; ++i0)
+#pragma unroll
+            for (int i1 = 0; i1 < N1; ++i1)
+                tile[lane * NP + i0 * N1 + i1] = __dmul_rn(__dmul_rn(1.0, t0v[i0]), t1v[i1]);
+        __syncwarp();
+        double *o = out + (e * P + p0) * N;
+        for (int idx = lane; idx < np * N; idx += 32)
+        {
+            const int row = idx / N, col = idx - row * N;
+            __stcs(o + idx, tile[row * NP + col]);
+        }
+    }
+}
+
+template <int N0, int N1>
+static void launch_points_eval_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out)
+{
+    constexpr int NP = (N0 * N1) | 1;
+    const size_t smem = sizeof(double) * (2 * N0 + 2 * N1 + 4 * 32 * NP);
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(points_evaluate_reg2d_kernel<N0, N1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t total_warps = E * ((P + 31) / 32);
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, 200 * 1024 / (smem + 1024)));
+    const int grid = (int)std::min<size_t>((total_warps + 3) / 4, (size_t)cfg.sm_count * per_sm);
+    points_evaluate_reg2d_kernel<N0, N1><<<grid, kPtRegThreads, smem, cfg.stream>>>(op, E, P, x, out);
+}
+
 // the instantiated shapes: n0, n1 <= 8 and |n0 - n1| <= 1 (isotropic spaces and the k-form component spaces p x (p+1))
 static bool dispatch_points_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *dofs, const double *x,
                                   int n_fields, const PointMasks &pm, double *out)
@@ -533,6 +598,22 @@ static bool dispatch_points_reg2d(const LaunchCfg &cfg, const PointOp &op, size_
 #define IB_PT_CASE(A, B)                                                                                                        \
     case (A) * 16 + (B):                                                                                                        \
         launch_points_reg2d<A, B>(cfg, op, E, P, dofs, x, n_fields, pm, out);                                                    \
+        return true;
+#define IB_PT_ROW(A) IB_PT_CASE(A, A) IB_PT_CASE(A, A + 1) IB_PT_CASE(A + 1, A)
+    switch (op.dim[0].n * 16 + op.dim[1].n)
+    {
+        IB_PT_ROW(1) IB_PT_ROW(2) IB_PT_ROW(3) IB_PT_ROW(4) IB_PT_ROW(5) IB_PT_ROW(6) IB_PT_ROW(7) IB_PT_CASE(8, 8)
+    }
+#undef IB_PT_ROW
+#undef IB_PT_CASE
+    return false;
+}
+
+static bool dispatch_points_eval_reg2d(const LaunchCfg &cfg, const PointOp &op, size_t E, size_t P, const double *x, double *out)
+{
+#define IB_PT_CASE(A, B)                                                                                                        \
+    case (A) * 16 + (B):                                                                                                        \
+        launch_points_eval_reg2d<A, B>(cfg, op, E, P, x, out);                                                                   \
         return true;
 #define IB_PT_ROW(A) IB_PT_CASE(A, A) IB_PT_CASE(A, A + 1) IB_PT_CASE(A + 1, A)
     switch (op.dim[0].n * 16 + op.dim[1].n)
@@ -964,6 +1045,16 @@ int launch_points_evaluate(const LaunchCfg &cfg, const PointOp &op, size_t E, si
     for (int k = 0; k < op.ndim; ++k)
         if (op.dim[k].n > PT_MAXN)
             return ib200_fail(IB200_ERROR_UNSUPPORTED, "arbitrary-point evaluation supports orders up to %d", PT_MAXN - 1);
+    const auto has_roots = [](int type) { return type != BASIS_LEGENDRE && type != BASIS_BERNSTEIN; };
+    if (op.ndim == 2 && has_roots(op.dim[0].type) && has_roots(op.dim[1].type) && !getenv("IB200_POINTS_NO_REG") &&
+        dispatch_points_eval_reg2d(cfg, op, E, P, x, out))
+    {
+        ++*cfg.launch_counter;
+        const cudaError_t err = cudaGetLastError();
+        if (err != cudaSuccess)
+            return ib200_fail(IB200_ERROR_CUDA, "launch of points_evaluate_reg2d_kernel failed: %s", cudaGetErrorString(err));
+        return INTERP_SUCCESS;
+    }
     int PB = 0;
     dim3 grid;
     const size_t smem = coop_shape(cfg, op, E, P, false, false, &PB, &grid);

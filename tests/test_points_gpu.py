@@ -87,6 +87,13 @@ def test_points_register_kernel_is_bit_identical_to_the_cooperative_one(ctx, orc
         ref = orc.reconstruct_points(basis, dofs, x, masks)
         for f in range(len(masks)):
             assert _err(got[:, f], ref[:, f]) < TOL, f"masks {masks} field {f}"
+    # FunctionSpace.evaluate: warp-per-32-points register kernel against the cooperative one and the oracle
+    phi = ctx.evaluate_points(basis, x)
+    monkeypatch.setenv("IB200_POINTS_NO_REG", "1")
+    phi_coop = ctx.evaluate_points(basis, x)
+    monkeypatch.delenv("IB200_POINTS_NO_REG")
+    assert np.array_equal(phi, phi_coop)
+    assert _err(phi, orc.evaluate_points(basis, x)) < TOL
 
 
 def test_points_empty_and_bad_arguments(ctx):

@@ -110,6 +110,12 @@ def main():
     ms = timed(ctx, lambda: ctx.reconstruct_points(basis, d_u.ptr, d_x.ptr, [0, 1, 2], out=d_o.ptr, where=DEVICE, n_elements=E,
                                                    n_points=P))
     report("N2 reconstruct_points p=6, 64 points, value+gradient", E, 8 * (cfg.N + 2 * P + 3 * P), ms)
+    # ---- N2: FunctionSpace.evaluate -- all N basis values at 64 points per element, 2^16 elements (1.6 GB out)
+    Ee = 1 << 16
+    d_phi = ctx.alloc(Ee * P * cfg.N * 8)
+    ms = timed(ctx, lambda: ctx.evaluate_points(basis, d_x.ptr, out=d_phi.ptr, where=DEVICE, n_elements=Ee, n_points=P))
+    report("N2 evaluate_points p=6, 64 points (basis values [E][P][N])", Ee, 8 * (2 * P + P * cfg.N), ms)
+    d_phi.free()
     # ---- N3: derivative DoFs along dimension 0 and 1, C2 space, 2^20 elements
     for b in (d_u, d_x, d_o):
         b.free()
