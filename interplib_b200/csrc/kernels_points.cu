@@ -553,12 +553,27 @@ __global__ void __launch_bounds__(kPtRegThreads)
     const size_t groups = (P + 31) / 32, total = E * groups;
     const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
     const size_t n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    // the coordinates of the NEXT group are requested before this one's tile is written and copied out
+    const auto fetch = [&](size_t it, double &c0, double &c1) {
+        c0 = c1 = 0.0;
+        if (it < total)
+        {
+            const size_t e = it / groups, p0 = (it - e * groups) * 32;
+            if (p0 + lane < P)
+            {
+                c0 = __ldcs(x + e * 2 * P + p0 + lane);
+                c1 = __ldcs(x + e * 2 * P + P + p0 + lane);
+            }
+        }
+    };
+    double nx0, nx1;
+    fetch(warp, nx0, nx1);
     for (size_t it = warp; it < total; it += n_warps)
     {
         const size_t e = it / groups, p0 = (it - e * groups) * 32;
         const int np = (int)((P - p0) < 32 ? (P - p0) : 32);
-        const double *xe = x + e * 2 * P + p0;
-        const double x0 = lane < np ? __ldcs(xe + lane) : 0.0, x1 = lane < np ? __ldcs(xe + P + lane) : 0.0;
+        const double x0 = nx0, x1 = nx1;
+        fetch(it + n_warps, nx0, nx1);
         double t0v[N0], t0d[N0], t1v[N1], t1d[N1];
         pt_lagrange_reg<N0>(r0, v0, x0, false, t0v, t0d);
         pt_lagrange_reg<N1>(r1, v1, x1, false, t1v, t1d);
