@@ -449,6 +449,15 @@ def main() -> int:
     if rank == 0:
         sampler.start()
         time.sleep(0.25)
+    barrier()
+    # the W warm-up steps of a short step (C2: 0.3 ms) end long before the SM clocks have come up from idle, and the
+    # sampler's start-up pause lets them fall again: keep stepping, untimed, until the GPU has been busy for 0.2 s
+    t_warm, warm_run = time.perf_counter(), args.warmup
+    while time.perf_counter() - t_warm < 0.2:
+        for _ in range(8):
+            wl.step_device()
+        ctx.synchronize()
+        warm_run += 8
     launches0 = ctx.stats()["kernel_launches"]
     barrier()
     ctx.timer_start(0)
@@ -522,7 +531,8 @@ def main() -> int:
             "config": {"workload": f"{cfg.name}: {cfg.description}", "elements_per_gpu": wl.E, "basis": [list(b) for b in cfg.basis],
                        "rule": [list(r) for r in cfg.rules], "l2": "inputs+outputs larger than L2 "
                        f"({(wl.bytes_per_elem * wl.E) >> 20} MiB per step vs 126 MB L2)", "device": info["name"],
-                       "sm_count": info["sm_count"], "parallelism": f"element-partitioned x{world}, no data-path collective"},
+                       "sm_count": info["sm_count"], "parallelism": f"element-partitioned x{world}, no data-path collective",
+                       "warmup_steps_run": warm_run},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
