@@ -847,7 +847,7 @@ __device__ __forceinline__ void chol_diag32(double *D, double *rinv_out, int lan
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
     spd_solve_blocked_kernel(int n, int lda, bool staged, size_t E, double *__restrict__ mass, double *__restrict__ rhs)
 {
     extern __shared__ __align__(16) double chol_blk_smem[];
@@ -937,7 +937,20 @@ __global__ void __launch_bounds__(256)
                 while (ti * (ti + 1) / 2 > t)
                     --ti;
                 const int tj = t - ti * (ti + 1) / 2;
-                double acc[4][4] = {};
+                // the tile of A is requested first: its latency (L2 or HBM for the in-place mode) hides behind the 32 steps
+                double acc[4][4];
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+                {
+                    const int i = k1 + 4 * ti + a;
+                    const double *row = i < n ? A + (size_t)i * lda : brow;
+#pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                    {
+                        const int j = k1 + 4 * tj + b;
+                        acc[a][b] = (i <= n && j < n && j <= i) ? row[j] : 0.0;
+                    }
+                }
                 const double *pi = PT + 4 * ti, *pj = PT + 4 * tj;
 #pragma unroll 8
                 for (int m = 0; m < kCholNB; ++m)
@@ -951,7 +964,7 @@ __global__ void __launch_bounds__(256)
                     for (int a = 0; a < 4; ++a)
 #pragma unroll
                         for (int b = 0; b < 4; ++b)
-                            acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+                            acc[a][b] = fma(-av[a], bv[b], acc[a][b]);
                 }
 #pragma unroll
                 for (int a = 0; a < 4; ++a)
@@ -965,7 +978,7 @@ __global__ void __launch_bounds__(256)
                     {
                         const int j = k1 + 4 * tj + b;
                         if (j < n && j <= i)
-                            row[j] -= acc[a][b];
+                            row[j] = acc[a][b];
                     }
                 }
             }
