@@ -991,6 +991,14 @@ __global__ void __launch_bounds__(256, 2)
         for (int kb = ((n - 1) / kCholNB) * kCholNB; kb >= 0; kb -= kCholNB)
         {
             const int nb = n - kb < kCholNB ? n - kb : kCholNB;
+            // the factor's diagonal block into shared memory first: warp 0's 32 dependent steps then wait on LDS, not on L2
+            for (int idx = tid; idx < nb * nb; idx += nthr)
+            {
+                const int i = idx / nb, j = idx - i * nb;
+                if (j < i)
+                    D[i * kCholLD + j] = A[(size_t)(kb + i) * lda + kb + j];
+            }
+            __syncthreads();
             if (tid < 32)
             {
                 double yv = lane < nb ? y[kb + lane] : 0.0;
@@ -1001,7 +1009,7 @@ __global__ void __launch_bounds__(256, 2)
                     if (lane == k)
                         yv = uk;
                     else if (lane < k)
-                        yv = fma(-A[(size_t)(kb + k) * lda + kb + lane], uk, yv);
+                        yv = fma(-D[k * kCholLD + lane], uk, yv);
                 }
                 if (lane < nb)
                     y[kb + lane] = yv;
