@@ -13,7 +13,7 @@ done
 B="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e"
 for w in ${NCU_WORKLOADS:-}; do
   $B --workload $w > gpurun_out/plain_$w.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -c 80 --csv --log-file gpurun_out/launches_$w.csv $B --workload $w > gpurun_out/ncu_list_$w.log 2>&1
+  ncu --metrics gpu__time_duration.sum --clock-control none -c ${NCU_LIST_COUNT:-80} --csv --log-file gpurun_out/launches_$w.csv $B --workload $w > gpurun_out/ncu_list_$w.log 2>&1
   $B --workload $w > gpurun_out/plain_$w.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-eval2d|mass2d}" -s ${NCU_SKIP:-3} -c 1 -f -o gpurun_out/prof_$w $B --workload $w > gpurun_out/ncu_full_$w.log 2>&1
   tail -2 gpurun_out/ncu_full_$w.log | cut -c1-300
