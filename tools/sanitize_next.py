@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
-"""Small driver for compute-sanitizer (memcheck / racecheck) over the round-1f kernels: register and blocked Cholesky,
-bulk-copy derivative kernel, register point kernel, fused projection.   compute-sanitizer --tool racecheck python tools/sanitize_next.py"""
+"""Small-case driver over the round-1f kernels (register, two-block and blocked Cholesky, bulk-copy derivative kernel,
+register point kernels, fused projection) with ragged sizes: run it plainly for a quick check against NumPy, or under
+`compute-sanitizer --tool memcheck|racecheck` on a machine where that tool is available (it is closed on the round's GPU pool)."""
 import sys
 from pathlib import Path
 
