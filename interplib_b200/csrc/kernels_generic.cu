@@ -1176,13 +1176,16 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
         ++*cfg.launch_counter;
         return check_launch("spd_solve_reg2_kernel");
     }
-    if (!getenv("IB200_SPD_NO_BLOCKED"))
+    const bool staged = n <= 127;
+    const int lda = staged ? ((int)n | 1) : (int)n;
+    const int RP = ((int)n + 1 + 3) & ~3, vec = ((int)n + kCholNB + 1) & ~1;
+    const size_t smem_blocked = sizeof(double) * (((kCholNB * kCholLD + 1) & ~1) + (size_t)kCholNB * RP + 2 * vec +
+                                                  (staged ? (size_t)(n + 1) * lda : 0));
+    // the transposed panel of the blocked kernel holds 32 x (n + 1) doubles: systems beyond n ~ 740 do not fit 200 KB of
+    // shared memory and take the warp-per-element in-place kernel below
+    if (smem_blocked <= 200 * 1024 && !getenv("IB200_SPD_NO_BLOCKED"))
     {
-        const bool staged = n <= 127;
-        const int lda = staged ? ((int)n | 1) : (int)n;
-        const int RP = ((int)n + 1 + 3) & ~3, vec = ((int)n + kCholNB + 1) & ~1;
-        const size_t smem = sizeof(double) * (((kCholNB * kCholLD + 1) & ~1) + (size_t)kCholNB * RP + 2 * vec +
-                                              (staged ? (size_t)(n + 1) * lda : 0));
+        const size_t smem = smem_blocked;
         const int threads = n <= 64 ? 128 : 256;
         IB_CUDA(cudaFuncSetAttribute(spd_solve_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         int per_sm = 0;
