@@ -1,23 +1,32 @@
 #!/usr/bin/env python3
-"""bench.py -- throughput of the interplib hot path on B200 (contract: see README / DESIGN.md section 6).
+"""bench.py -- throughput of the interplib hot path on B200 (contract: DESIGN.md section 6).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c5|c4|c3|c1] [--impl ours|reference]
 
-One "step" = one pass of the hot path over one batch of synthetic elements.  The default workload is
-BASELINE.json config 2 (2-D quads, 2^20 elements, p=6, basis + gradient evaluation at 8x8 Gauss points, FP64);
-metric = elements (basis+grad evals) per second, whole job.  Elements are independent: under torchrun every rank
-owns a GPU and its own slab of elements (weak scaling, no data-path collective); timing is on the device (CUDA
-events on the launching stream), max over ranks.  Rank 0 prints ONE JSON line.
+One "step" = one pass of the hot path over one batch of synthetic elements.  BASELINE.json's metric has two halves,
+"basis+grad evals/s" and "element mass matrices/s"; the default run reports both in ONE JSON line:
+
+* headline (`metric`, `value`, `roofline`, `e2e`, `cpu_baseline`): BASELINE config 2 -- 2-D quads, 2^20 elements per
+  GPU, p=6, value + gradient at 8x8 Gauss points, FP64; weak scaling, no data-path collective;
+* `mass`:   BASELINE config 5's element work on one 2^22-element slab per GPU -- 25x25 mass matrix + L2 right-hand side
+  per element (`element_mass_matrices_per_s`), with its own `roofline`, `e2e` and `cpu_baseline`;
+* `strong`: BASELINE config 5 as the north star states it -- 2^24 quads in total, block-partitioned over the N ranks,
+  every rank runs the whole L2 projection of its elements (geometry + f in, primal DoFs out; mass matrices assembled
+  and solved on the device) and the ranks then ALL-GATHER the [E,25] primal DoFs and ALL-REDUCE the projection norm
+  over NCCL through the C ABI, all inside the CUDA-event region (`"scaling": "strong"` inside the record).
+
+Elements are independent: under torchrun every rank owns a GPU; timing is on the device (CUDA events on the launching
+stream), max over ranks.  Rank 0 prints the line.  torch is used for the launcher's barrier and the max over ranks
+only; everything measured goes through libinterp_b200.so.
 
 `--impl reference` times the reference's own CPU implementation (oracle/_ref: the unmodified interplib extension
-driven per element through its Python API, fanned out over all host cores; falls back to the C oracle port when
-the compiled reference is absent) on a bounded sample of the same workload.
+driven per element through its Python API, one spawned worker process per host core; the C oracle port when the
+compiled reference is absent) on a bounded sample of the same workloads and prints the same keys.
 """
 from __future__ import annotations
 
 import argparse
 import json
-import math
 import os
 import subprocess
 import sys
@@ -30,7 +39,7 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
-from interplib_b200 import synthetic as syn  # noqa: E402
+from interplib_b200 import synthetic as syn  # noqa: E402  (pure NumPy: does not load libinterp_b200.so)
 
 # ncu-measured DRAM traffic of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum of one launch from the
 # `ncu --set full` captures summarised under profiles/*_full.txt) as (bytes per launch, elements in that launch); the
@@ -43,6 +52,10 @@ NCU_TRAFFIC_BYTES = {
     "c3": (11733279000, 1 << 18),  # profiles/r01e_c3_mass2d_full.txt
     "c1": None,
 }
+METRIC = {"c2": "basis_grad_evals_per_s"}
+DEFAULT_ELEMENTS = {"c1": 1024, "c2": 1 << 20, "c3": 1 << 18, "c4": 1 << 16, "c5": 1 << 22}
+# sum-factorised FP64 operation counts per element
+FLOPS_PER_ELEMENT = {"c2": 2 * (2 * 7 * 7 * 8 + 3 * 7 * 8 * 8), "c4": 3.31e6, "c5": 10.9e3, "c3": 0.50e6}
 
 
 def peaks():
@@ -51,6 +64,25 @@ def peaks():
         d = json.loads(p.read_text())
         return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def fp64_peak():
+    """Measured FP64 peaks of this pool's B200 (tools/fp64_peak.cu -> profiles/r01_fp64_peak.json)."""
+    p = ROOT / "profiles" / "r01_fp64_peak.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["fp64_fma_tflops"]), float(d["fp64_dmma_m8n8k4_tflops"]), "measured (profiles/r01_fp64_peak.json)"
+    return 37.0, 37.0, "nominal"
+
+
+def workload_config(name: str, elements_per_gpu: int) -> dict:
+    """The `config` object: names the workload only, so the repo arm and the reference arm print the same one."""
+    cfg = syn.CONFIGS[name]
+    per_elem = {"c2": 8 * (cfg.N + 3 * cfg.Q), "c3": 8 * (8 + 4 * 72 * 72)}.get(name, 8 * (8 + cfg.Q + cfg.N * cfg.N + cfg.N))
+    return {"workload": f"{cfg.name}: {cfg.description}", "elements_per_gpu": int(elements_per_gpu),
+            "basis": [list(b) for b in cfg.basis], "rule": [list(r) for r in cfg.rules],
+            "l2": f"inputs+outputs larger than L2 ({(per_elem * elements_per_gpu) >> 20} MiB per step vs 126 MB L2)",
+            "parallelism": "element-partitioned, one rank per GPU, no data-path collective in this step"}
 
 
 # ------------------------------------------------------------------------------------------------ workloads
@@ -62,11 +94,14 @@ class Workload:
         self.cfg = cfg = syn.CONFIGS[name]
         self.ctx = ctx
         self.basis, self.rules, self.gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
-        E = n_elements or self.default_elements()
+        E = n_elements or DEFAULT_ELEMENTS[name]
         self.E = E
         N, Q = cfg.N, cfg.Q
         rng = np.random.default_rng(2 + rank)
         self.blocks = None
+        self.unit = "elements/s"
+        self.metric = METRIC.get(name, "element_mass_matrices_per_s")
+        self.flops_per_elem = FLOPS_PER_ELEMENT.get(name)
         if name == "c2":
             # basis + gradient eval: dofs[E][49] -> out[E][3][64]
             self.h_in = {"dofs": rng.random((E, N))}
@@ -74,12 +109,10 @@ class Workload:
             self.bytes_per_elem = 8 * (N + 3 * Q)
             self.dominant = "eval2d_kernel (K1: value + gradient)"
             self.dominant_bytes_per_elem = self.bytes_per_elem
-            self.flops_per_elem = 2 * (2 * 7 * 7 * 8 + 3 * 7 * 8 * 8)
-            self.metric = "basis_grad_evals_per_s"
-            self.unit = "elements/s"
+            self.dominant_is_step = True
         elif name == "c3":
             # the four determinant-weighted blocks M_ab = compute_mass_matrix(space_b, space_a, smap) of the 2-D 1-form
-            # basis (SURVEY 8c caveat): geometry[E][2][4] -> 4 x M[E][72][72] (= the 144 x 144 element matrix, block-wise)
+            # basis (SURVEY 8c caveat): geometry[E][2][4] -> M[E][144][144] in ONE launch (ib200_kform_mass_mapped_batch)
             first = (rank * E) % max(cfg.n_elements - E + 1, 1)
             self.h_in = {"geom": syn.geometry(cfg, first=first, count=E)}
             self.blocks = [(a, b, list(sa), list(sb)) for a, sa in enumerate(syn.C3_SPACES) for b, sb in enumerate(syn.C3_SPACES)]
@@ -87,36 +120,38 @@ class Workload:
             self.bytes_per_elem = 8 * (8 + 4 * 72 * 72)
             self.dominant = "mass2d_kernel (K2, one 72x72 block per launch, 4 launches per step)"
             self.dominant_bytes_per_elem = 8 * (8 + 72 * 72)
-            self.metric = "element_mass_matrices_per_s"
-            self.unit = "elements/s"
+            self.dominant_is_step = False
         else:
             # mass matrix (+ L2 right-hand side): geometry[E][2][4] (+ f[E][Q]) -> M[E][N][N] (+ b[E][N])
             first = (rank * E) % max(cfg.n_elements - E + 1, 1)
             if cfg.ndim == 2:
                 geom = syn.geometry(cfg, first=first, count=E)
             else:
-                geom = _slab(cfg, 0, E)
-            self.h_in = {"geom": geom, "fvals": rng.standard_normal((E, Q))}
+                geom = syn.geometry(cfg)[(np.arange(E)) % cfg.n_elements]
+            self.h_in = {"geom": np.ascontiguousarray(geom), "fvals": rng.standard_normal((E, Q))}
             self.out_shapes = {"mass": (E, N, N), "rhs": (E, N)}
             self.bytes_per_elem = 8 * (geom[0].size + Q + N * N + N)
-            self.dominant = ({"c5": "mass2d_lo_kernel (K2-lo, geometry fused)", "c4": "mass2d_mma_kernel (K2-hi DMMA, geometry fused)"}
+            fused = name == "c5"  # low order: geometry + mass + right-hand side are ONE kernel, which is then the step
+            self.dominant = ({"c5": "mass2d_lo_kernel (K2-lo: geometry + mass matrix + L2 right-hand side fused)",
+                              "c4": "mass2d_mma_kernel (K2-hi DMMA, geometry fused)"}
                              .get(name, "mass2d_kernel (K2, geometry fused)") if cfg.ndim == 2 else "geometry + mass kernels (1-D generic)")
-            self.dominant_bytes_per_elem = 8 * (geom[0].size + N * N)
-            self.metric = "element_mass_matrices_per_s"
-            self.unit = "elements/s"
+            self.dominant_bytes_per_elem = self.bytes_per_elem if fused else 8 * (geom[0].size + N * N)
+            self.dominant_is_step = fused
         self.d_in = {k: ctx.alloc(v.nbytes).upload(v) for k, v in self.h_in.items()}
         self.d_out = {k: ctx.alloc(int(np.prod(s)) * 8) for k, s in self.out_shapes.items()}
+        self.pinned = []
 
-    def default_elements(self) -> int:
-        # the whole configuration per launch (C3: 2^18 elements, four 10.9 GB blocks; C4: 2^16 elements, 43.8 GB); C5's
-        # 16M quads x 5 kB = 84 GB are executed in slabs of 2^22 elements reusing one output slab
-        return {"c1": 1024, "c2": 1 << 20, "c3": 1 << 18, "c4": 1 << 16, "c5": 1 << 22}[self.name]
+    def free(self) -> None:
+        for b in list(self.d_in.values()) + list(self.d_out.values()):
+            b.free()
+        for p in self.pinned:
+            p.free()
+        self.h_in = self.d_in = self.d_out = None
 
     @property
     def E2(self) -> int:
         """Elements of one end-to-end step: the host-pointer path streams its arrays through PCIe in 16 MB chunks, so its
-        rate does not depend on the batch; C3-C5 use a slab of the device-resident batch to bound pinned host memory
-        (C3's four blocks of 2^18 elements would be 43 GB of pinned buffers)."""
+        rate does not depend on the batch; C3-C5 use a slab of the device-resident batch to bound pinned host memory."""
         return min(self.E, {"c3": 1 << 15, "c4": 1 << 13, "c5": 1 << 20}.get(self.name, self.E))
 
     def step_device(self, dominant_only: bool = False) -> None:
@@ -131,7 +166,7 @@ class Workload:
                 c.mass_matrix_mapped(sb, sa, self.rules, self.gb, self.d_in["geom"].ptr, 2, out=self.d_out[f"block_{a}{b}"].ptr,
                                      where=DEVICE, n_elements=self.E)
         else:
-            if dominant_only:
+            if dominant_only and not self.dominant_is_step:
                 c.mass_matrix_mapped(self.basis, self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys,
                                      out=self.d_out["mass"].ptr, where=DEVICE, n_elements=self.E)
                 return
@@ -140,14 +175,21 @@ class Workload:
             c.l2_system_mapped(self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys, self.d_in["fvals"].ptr,
                                mass=self.d_out["mass"].ptr, rhs=self.d_out["rhs"].ptr, where=DEVICE, n_elements=self.E)
 
-    # end to end through the public host-pointer API (pinned host buffers, H2D + D2H inside the call)
-    def e2e_prepare(self) -> None:
+    # ---- end to end through the public host-pointer API (pinned host buffers, H2D + D2H inside the call) ------------
+    def e2e_prepare(self, chain: bool = False) -> None:
         c = self.ctx
         n = self.E2
         self.p_in = {k: c.pinned((n,) + v.shape[1:]) for k, v in self.h_in.items()}
         for k, v in self.h_in.items():
             self.p_in[k].array[...] = v[:n]
-        self.p_out = {k: c.pinned((n,) + tuple(s[1:])) for k, s in self.out_shapes.items()}
+        shapes = {"primal": (n, self.cfg.N)} if chain else {k: (n,) + tuple(s[1:]) for k, s in self.out_shapes.items()}
+        self.p_out = {k: c.pinned(s) for k, s in shapes.items()}
+        self.pinned += list(self.p_in.values()) + list(self.p_out.values())
+
+    def e2e_release(self) -> None:
+        for p in self.pinned:
+            p.free()
+        self.pinned = []
 
     def step_e2e(self) -> float:
         c = self.ctx
@@ -162,12 +204,19 @@ class Workload:
                            mass=self.p_out["mass"].array, rhs=self.p_out["rhs"].array)
         return float(self.p_out["rhs"].array[-1, 0])
 
-    @property
+    def step_e2e_chain(self) -> float:
+        """projection_l2_primal of the slab through the host-pointer C ABI: geometry + f in, primal DoFs out; the mass
+        matrices are assembled, factorised and consumed on the device (ib200_l2_project_mapped_batch)."""
+        self.ctx.l2_project_mapped(self.basis, self.rules, self.gb, self.p_in["geom"].array, self.cfg.n_phys,
+                                   self.p_in["fvals"].array, out=self.p_out["primal"].array)
+        return float(self.p_out["primal"].array[-1, 0])
+
     def h2d_bytes(self) -> int:
         return int(sum(v.nbytes // self.E * self.E2 for v in self.h_in.values()))
 
-    @property
-    def d2h_bytes(self) -> int:
+    def d2h_bytes(self, chain: bool = False) -> int:
+        if chain:
+            return 8 * self.cfg.N * self.E2
         return int(sum(int(np.prod(s[1:])) * 8 * self.E2 for s in self.out_shapes.values()))
 
 
@@ -234,156 +283,362 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-# ------------------------------------------------------------------------------------------------ CPU arms
-def _slab(cfg, first: int, count: int) -> np.ndarray:
-    """geom_dofs of `count` elements starting at `first`, wrapping around the configuration's mesh."""
-    first %= cfg.n_elements
-    if cfg.ndim == 2 and first + count <= cfg.n_elements:
-        return syn.geometry(cfg, first=first, count=count)
-    if cfg.ndim == 1:
-        return np.ascontiguousarray(syn.geometry(cfg)[(first + np.arange(count)) % cfg.n_elements])
-    parts, left = [], count
-    while left > 0:
-        n = min(left, cfg.n_elements - first)
-        parts.append(syn.geometry(cfg, first=first, count=n))
-        first, left = 0, left - n
-    return np.concatenate(parts)
-
-
-def _ref_worker(args):
-    """Run the compiled reference per element on a slab (one process per core)."""
-    name, first, count, seed = args
-    from oracle import refdrive as rd
+# ------------------------------------------------------------------------------------------------ reference arm
+def _reference_record(name: str, steps: int, warmup: int, budget_s: float, elements_cfg: int) -> dict:
+    """Time the reference's CPU path on all host cores for one workload; every step is a bounded sample."""
+    from oracle.cpu_arm import CpuArm
 
     cfg = syn.CONFIGS[name]
-    basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
-    rng = np.random.default_rng(seed)
-    t0 = time.perf_counter()
-    if name == "c2":
-        rd.reconstruct(basis, rules, rng.random((count, cfg.N)), [0, 1, 2])
-    else:
-        geom = _slab(cfg, first, count)
-        t0 = time.perf_counter()
-        if name == "c3":
-            for sa in syn.C3_SPACES:
-                for sb in syn.C3_SPACES:
-                    rd.mass(list(sb), list(sa), rules, count, gb, geom, cfg.n_phys)
-        else:
-            rd.mass(basis, basis, rules, count, gb, geom, cfg.n_phys)
-            rd.l2_dual(basis, rules, rng.standard_normal((count, cfg.Q)), gb, geom, cfg.n_phys)
-    return time.perf_counter() - t0
-
-
-def _port_step(name, count, seed):
-    from oracle import oracle as orc
-
-    cfg = syn.CONFIGS[name]
-    basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
-    rng = np.random.default_rng(seed)
-    if name == "c2":
-        dofs = rng.random((count, cfg.N))
-        t0 = time.perf_counter()
-        orc.reconstruct(basis, rules, dofs, [0, 1, 2])
-        return time.perf_counter() - t0
-    geom = _slab(cfg, 0, count)
-    f = rng.standard_normal((count, cfg.Q))
-    t0 = time.perf_counter()
-    _, det, _ = orc.geometry(gb, rules, geom, cfg.n_phys, want_coords=False, want_jinv=False)
-    if name == "c3":
-        for sa in syn.C3_SPACES:
-            for sb in syn.C3_SPACES:
-                orc.mass(list(sb), list(sa), rules, count, det=det)
-    else:
-        orc.mass(basis, basis, rules, count, det=det)
-        orc.l2_dual(basis, rules, f, det=det)
-    return time.perf_counter() - t0
-
-
-class CpuArm:
-    """The reference's CPU path on this host: `reference` = unmodified compiled interplib, one process per core;
-    `port` = the C oracle restatement with OpenMP."""
-
-    def __init__(self, name: str, single_thread: bool = False):
-        from oracle import build_ref
-
-        self.name = name
-        self.kind = "reference" if build_ref.built() else "port"
-        self.cores = 1 if single_thread else (os.cpu_count() or 1)
-        self.pool = None
-        if self.kind == "reference" and self.cores > 1:
-            import multiprocessing as mp
-
-            self.pool = mp.get_context("fork").Pool(self.cores)
-        if self.kind == "port":
-            from oracle import oracle as orc
-
-            orc.build()
-            if single_thread:
-                os.environ["OMP_NUM_THREADS"] = "1"
-            self.cores = 1 if single_thread else orc.threads()
-
-    def run(self, count: int, seed: int = 0) -> float:
-        """Process `count` elements; returns wall seconds."""
-        t0 = time.perf_counter()
-        if self.kind == "port":
-            _port_step(self.name, count, seed)
-        elif self.pool is None:
-            _ref_worker((self.name, 0, count, seed))
-        else:
-            per = max(1, count // self.cores)
-            jobs = [(self.name, i * per, per, seed + i) for i in range(self.cores)]
-            self.pool.map(_ref_worker, jobs)
-        return time.perf_counter() - t0
-
-    def effective_count(self, count: int) -> int:
-        if self.pool is None:
-            return count
-        return max(1, count // self.cores) * self.cores
-
-    def calibrate(self, target_s: float) -> int:
-        """Elements per step so that one step takes about target_s."""
-        n = self.effective_count(max(self.cores * 4, 8))
-        t = self.run(n)
-        while t < 0.2 and n < (1 << 22):
-            n *= 4
-            t = self.run(n)
-        return self.effective_count(max(self.cores, int(n * target_s / max(t, 1e-9))))
-
-    def close(self):
-        if self.pool:
-            self.pool.close()
-            self.pool.join()
+    arm = CpuArm(name)
+    per_step = min(4.0, budget_s / max(steps + warmup, 1))
+    count = arm.calibrate(per_step, cap=elements_cfg)
+    for w in range(warmup):
+        arm.run(count, seed=100 + w)
+    t = [arm.run(count, seed=200 + k) for k in range(steps)]
+    arm.close()
+    total = float(np.sum(t))
+    value = count * steps / total
+    sample = (f"{count} elements per step of {cfg.name} ({cfg.description}); per-element calls through the "
+              f"{'compiled reference Python API, one spawned worker process per core' if arm.kind == 'reference' else 'C oracle port (OpenMP)'}")
+    return {"metric": METRIC.get(name, "element_mass_matrices_per_s"), "value": value, "unit": "elements/s",
+            "ms_per_step": 1e3 * total / steps, "steps": steps, "warmup": warmup,
+            "config": workload_config(name, elements_cfg),
+            "cpu_baseline": {"value": value, "unit": "elements/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
+            "e2e": {"value": value, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
 def run_reference_arm(args, rank: int, world: int) -> int:
     if rank != 0:
         return 0
     name = args.workload
-    cfg = syn.CONFIGS[name]
-    arm = CpuArm(name)
-    budget = 150.0  # seconds for warm-up + timed steps
-    per_step = min(3.0, budget / max(args.steps + args.warmup, 1))
-    count = arm.calibrate(per_step)
-    for w in range(args.warmup):
-        arm.run(count, seed=100 + w)
-    t = [arm.run(count, seed=200 + k) for k in range(args.steps)]
-    arm.close()
-    total = float(np.sum(t))
-    value = count * args.steps / total
-    sample = (f"{count} elements per step of {cfg.name} ({cfg.description}); per-element calls through the "
-              f"{'compiled reference Python API' if arm.kind == 'reference' else 'C oracle port'}")
-    line = {
-        "impl": "reference", "metric": "basis_grad_evals_per_s" if name == "c2" else "element_mass_matrices_per_s",
-        "value": value, "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{name}: {cfg.description}", "elements_per_step": count, "host_cores": arm.cores},
-        "cpu_baseline": {"value": value, "unit": "elements/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
-        "e2e": {"value": value, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
+    head = _reference_record(name, args.steps, args.warmup, 110.0, args.elements or DEFAULT_ELEMENTS[name])
+    line = {"impl": "reference", "metric": head["metric"], "value": head["value"], "unit": head["unit"], "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": head["config"],
+            "cpu_baseline": head["cpu_baseline"], "e2e": head["e2e"], "gpu_launches": 0}
+    if name == "c2" and not args.no_mass:
+        # the other half of the metric: config 5's per-element mass matrix + L2 right-hand side
+        line["mass"] = _reference_record("c5", 3, 1, 40.0, DEFAULT_ELEMENTS["c5"])
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+class Runner:
+    def __init__(self, args):
+        self.args = args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist_mod
+
+            torch.cuda.set_device(self.local_rank)
+            dist_mod.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+            self.dist = dist_mod
+        import interplib_b200 as ib
+
+        self.numa = bind_to_gpu_numa_node(self.local_rank)
+        self.ctx = ib.Context(self.local_rank)
+        self.info = self.ctx.info()
+        self.hbm_peak, self.peak_src = peaks()
+
+    def barrier(self):
+        self.ctx.synchronize()
+        if self.dist is not None:
+            import torch
+
+            self.dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        if self.dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{self.local_rank}")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def keep_busy(self, step, seconds: float = 0.2) -> int:
+        """A short step's W warm-ups end long before the SM clocks have come up from idle: keep stepping, untimed, until
+        the GPU has been busy for `seconds` right before the timed region.  Returns the extra steps run."""
+        t0, n = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds:
+            for _ in range(8):
+                step()
+            self.ctx.synchronize()
+            n += 8
+        return n
+
+    # ---- one workload: device-resident value + roofline + e2e + CPU baseline ------------------------------------------
+    def measure(self, name: str, steps: int, warmup: int, elements: int | None, sample_clocks: bool, chain_e2e: bool) -> dict:
+        args, ctx, rank, world = self.args, self.ctx, self.rank, self.world
+        wl = Workload(name, ctx, rank, elements)
+        for _ in range(warmup):
+            wl.step_device()
+        self.barrier()
+        sampler = ClockSampler()
+        if rank == 0 and sample_clocks:
+            sampler.start()
+            time.sleep(0.25)
+        self.barrier()
+        warm_run = warmup + self.keep_busy(wl.step_device)
+        launches0 = ctx.stats()["kernel_launches"]
+        self.barrier()
+        ctx.timer_start(0)
+        for _ in range(steps):
+            wl.step_device()
+        ctx.timer_stop(0)
+        self.barrier()
+        ms_total_local = ctx.timer_ms(0)
+        ms_total = self.max_over_ranks(ms_total_local)
+        launches = ctx.stats()["kernel_launches"] - launches0
+        clocks = sampler.stop(set(range(world))) if (rank == 0 and sample_clocks) else None
+        ms_step = ms_total / steps
+        value = wl.E * world / (ms_step * 1e-3)
+
+        # average launch duration of the dominant kernel: when the step IS that kernel (C2: one eval2d launch; C5: the fused
+        # geometry + mass + right-hand-side launches) it comes from the step's own timed region, otherwise from a second
+        # CUDA-event region of the same length around that kernel alone (outputs larger than L2: no cache hits between launches)
+        if wl.dominant_is_step:
+            dom_launches, dom_ms_total, n_dom = launches, ms_total_local, steps
+        else:
+            n_dom = steps
+            before = ctx.stats()["kernel_launches"]
+            ctx.timer_start(1)
+            for _ in range(n_dom):
+                wl.step_device(dominant_only=True)
+            ctx.timer_stop(1)
+            dom_launches = ctx.stats()["kernel_launches"] - before
+            dom_ms_total = ctx.timer_ms(1)
+        kernel_ms = dom_ms_total / max(dom_launches, 1)
+        el_per_launch = wl.E * n_dom / max(dom_launches, 1)
+        achieved = wl.dominant_bytes_per_elem * el_per_launch / (kernel_ms * 1e-3) / 1e9
+        traffic = NCU_TRAFFIC_BYTES.get(name)
+        if traffic is not None:
+            traffic = int(round(traffic[0] * (el_per_launch / traffic[1])))
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": self.hbm_peak, "unit": "GB/s", "frac": achieved / self.hbm_peak,
+                    "traffic": traffic, "peak_source": self.peak_src, "kernel": wl.dominant,
+                    "algorithmic_bytes_per_element": wl.dominant_bytes_per_elem,
+                    "step_algorithmic_bytes_per_element": wl.bytes_per_elem,
+                    "step_frac": wl.bytes_per_elem * wl.E / (ms_total_local / steps * 1e-3) / 1e9 / self.hbm_peak,
+                    "elements_per_launch": el_per_launch, "kernel_ms": kernel_ms,
+                    "kernel_ms_source": "the step's own CUDA-event region" if wl.dominant_is_step else "separate CUDA-event region, dominant kernel alone",
+                    "fp64_flops_per_element": wl.flops_per_elem}
+        if wl.flops_per_elem:
+            fma, dmma, src = fp64_peak()
+            tf = wl.flops_per_elem * wl.E / (ms_total_local / steps * 1e-3) / 1e12
+            roofline.update({"fp64_tflops": tf, "fp64_peak_tflops": dmma if name == "c4" else fma, "fp64_frac": tf / (dmma if name == "c4" else fma),
+                             "fp64_peak_source": src})
+
+        # ---- end to end through the host-pointer API (pinned host buffers) ----------------------------------------------
+        def time_e2e(step, n):
+            step()
+            self.barrier()
+            t0 = time.perf_counter()
+            for _ in range(n):
+                step()
+            self.barrier()
+            return self.max_over_ranks(time.perf_counter() - t0)
+
+        e2e = e2e_full = None
+        if not args.no_e2e:
+            n_e2e = args.e2e_steps or max(3, min(steps, 10))
+            note = {"steps": n_e2e, "elements_per_step": wl.E2, "cpu_affinity": self.numa,
+                    "timing": "host wall clock around the synchronous C-ABI call with pinned host buffers, max over ranks"}
+            wl.e2e_prepare(chain=False)
+            dt = time_e2e(wl.step_e2e, n_e2e)
+            e2e_full = {"value": wl.E2 * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes(),
+                        "d2h_bytes_per_step": wl.d2h_bytes(), "ms_per_step": 1e3 * dt / n_e2e, **note,
+                        "path": "every output array of the step travels to the host"}
+            wl.e2e_release()
+            e2e = e2e_full
+            if chain_e2e:
+                wl.e2e_prepare(chain=True)
+                dt = time_e2e(wl.step_e2e_chain, n_e2e)
+                e2e = {"value": wl.E2 * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes(),
+                       "d2h_bytes_per_step": wl.d2h_bytes(chain=True), "ms_per_step": 1e3 * dt / n_e2e, **note,
+                       "path": "chained projection (ib200_l2_project_mapped_batch): geometry + f in, primal DoFs out; the "
+                               "element mass matrices are assembled and consumed on the device and never cross PCIe"}
+                wl.e2e_release()
+
+        # ---- CPU baseline beside it (rank 0, N=1 only) ------------------------------------------------------------------
+        cpu = None
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:
+            from oracle.cpu_arm import CpuArm
+
+            arm = CpuArm(name, single_thread=True)
+            count = arm.calibrate(10.0)
+            t = arm.run(count, seed=7)
+            arm.close()
+            cpu = {"value": count / t, "unit": wl.unit, "cores": arm.cores, "kind": arm.kind,
+                   "sample": f"{count} elements of {name} in {t:.1f} s, per-element calls, single thread (the reference "
+                             "holds the GIL and has no parallel region)"}
+        rec = {"metric": wl.metric, "value": value, "unit": wl.unit, "steps": steps, "warmup": warmup, "ms_per_step": ms_step,
+               "config": workload_config(name, wl.E), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+               "gpu_launches": int(launches) * world, "clocks": clocks,
+               "run": {"device": self.info["name"], "sm_count": self.info["sm_count"], "warmup_steps_run": warm_run}}
+        if chain_e2e and e2e_full is not None:
+            rec["e2e_full_outputs"] = e2e_full
+        wl.free()
+        return rec
+
+    # ---- BASELINE config 5 as a strong-scaling job with the NCCL gather / reduce inside the timed region -----------------
+    def measure_strong(self, total_elements: int, steps: int, warmup: int) -> dict:
+        from interplib_b200 import DEVICE
+        from interplib_b200.partition import ElementPartition, NcclComm
+
+        ctx, rank, world = self.ctx, self.rank, self.world
+        cfg = syn.CONFIGS["c5"]
+        basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
+        N, Q = cfg.N, cfg.Q
+        comm = NcclComm.from_environment(ctx)
+        part = ElementPartition.from_comm(total_elements, comm)
+        base_n = min(1 << 20, total_elements)
+        f_base = np.random.default_rng(99).standard_normal((base_n, Q))  # f[e] = f_base[e mod 2^20]: the same on every rank
+
+        def upload_inputs(first: int, count: int):
+            d_g = ctx.alloc(max(count, 1) * 64)
+            d_f = ctx.alloc(max(count, 1) * Q * 8)
+            done = 0
+            while done < count:  # geometry of the real 4096 x 4096 jittered mesh, generated in slabs
+                n = min(1 << 21, count - done)
+                g = syn.geometry(cfg, first=first + done, count=n)
+                ctx_copy_h2d(ctx, int(d_g) + done * 64, g)
+                done += n
+            done = 0
+            while done < count:
+                lo = (first + done) % base_n
+                n = min(base_n - lo, count - done)
+                ctx_copy_h2d(ctx, int(d_f) + done * Q * 8, f_base[lo : lo + n])
+                done += n
+            return d_g, d_f
+
+        d_all = ctx.alloc(total_elements * N * 8)      # the gathered [E][25] primal DoFs, every rank
+        n_sub = 4                                       # sub-slabs per rank: the gather of one overlaps the compute of the next
+        sub = -(-part.max_count // n_sub)
+        d_norm = ctx.alloc(8 * n_sub)
+
+        def job(d_g, d_f, d_b, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub):
+            """Projection of `count` elements starting at global element `first` (this rank's slab, or everything for the
+            single-rank reference), pipelined in n_sub sub-slabs."""
+            for k in range(n_sub):
+                lo, hi = min(count, k * sub), min(count, (k + 1) * sub)
+                if hi > lo and compute:
+                    g, f = int(d_g) + lo * 64, int(d_f) + lo * Q * 8
+                    u = int(d_all) + (first + lo) * N * 8
+                    b = int(d_b) + lo * N * 8
+                    ctx.l2_dual_mapped(basis, rules, gb, g, cfg.n_phys, f, out=b, where=DEVICE, n_elements=hi - lo)
+                    ctx.l2_project_mapped(basis, rules, gb, g, cfg.n_phys, f, out=u, where=DEVICE, n_elements=hi - lo)
+                    ctx.dot(b, u, out=int(d_norm) + 8 * k, where=DEVICE, n=(hi - lo) * N)
+                if collectives:
+                    counts, offsets = part.slab_layout(N, k * sub, sub)
+                    comm.allgatherv(int(d_all) + (part.first + min(part.count, k * sub)) * N * 8, d_all, counts, offsets, overlap=True)
+            if collectives:
+                comm.allreduce_sums(int(d_norm), n_sub)
+                comm.join()
+
+        def timed(fn, k_steps):
+            self.barrier()
+            ctx.timer_start(2)
+            for _ in range(k_steps):
+                fn()
+            ctx.timer_stop(2)
+            self.barrier()
+            return self.max_over_ranks(ctx.timer_ms(2)) / k_steps
+
+        d_g, d_f = upload_inputs(part.first, part.count)
+        d_b = ctx.alloc(max(part.count, 1) * N * 8)
+        run_all = lambda: job(d_g, d_f, d_b, part.first, part.count, True)  # noqa: E731
+        for _ in range(max(warmup, 3)):
+            run_all()
+        launches0 = ctx.stats()["kernel_launches"]
+        ms_step = timed(run_all, steps)
+        launches = ctx.stats()["kernel_launches"] - launches0
+        ms_compute = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, False), steps)
+        ms_coll = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, True, compute=False), steps)
+        comm.check()
+        norms = d_norm.download((n_sub,))
+        proj_sq = float(np.sum(norms))
+
+        # ---- parity of the collective: a 4096-element slab owned by the LAST rank, recomputed by this rank alone, must equal
+        # the rows the all-gather delivered, bit for bit (GPUTEST boxes have one GPU: this is the driver-visible NCCL check)
+        run_all()
+        ctx.synchronize()
+        chk_n = min(4096, part.counts[-1])
+        chk_first = part.offsets[-1]
+        c_g, c_f = upload_inputs(chk_first, chk_n)
+        c_u = ctx.alloc(max(chk_n, 1) * N * 8)
+        ctx.l2_project_mapped(basis, rules, gb, int(c_g), cfg.n_phys, int(c_f), out=int(c_u), where=DEVICE, n_elements=chk_n)
+        ctx.synchronize()
+        mine = c_u.download((chk_n, N))
+        got = d_all.download((chk_n, N), offset_bytes=chk_first * N * 8)
+        parity_local = bool(np.array_equal(mine, got)) and bool(np.isfinite(got).all())
+        parity = self.max_over_ranks(0.0 if parity_local else 1.0) == 0.0
+        for b in (c_g, c_f, c_u, d_g, d_f, d_b):
+            b.free()
+
+        # ---- the same 2^24 elements on ONE GPU (rank 0 alone, no collective): the denominator of the strong-scaling efficiency
+        ms_single = None
+        if world > 1:
+            if rank == 0:
+                s_g, s_f = upload_inputs(0, total_elements)
+                s_b = ctx.alloc(total_elements * N * 8)
+                one = lambda: job(s_g, s_f, s_b, 0, total_elements, False, sub=-(-total_elements // n_sub))  # noqa: E731
+                for _ in range(2):
+                    one()
+                ctx.synchronize()
+                k1 = max(3, min(steps, 5))
+                ctx.timer_start(3)
+                for _ in range(k1):
+                    one()
+                ctx.timer_stop(3)
+                ms_single = ctx.timer_ms(3) / k1
+                for b in (s_g, s_f, s_b):
+                    b.free()
+            self.barrier()
+            ms_single = self.max_over_ranks(ms_single or 0.0)
+        else:
+            ms_single = ms_compute
+        nccl = comm.info()["nccl_version"]
+        comm.close()
+        d_all.free()
+        d_norm.free()
+        gather_bytes_in = (total_elements - part.max_count) * N * 8  # bytes every GPU receives
+        rec = {
+            "metric": "l2_projections_per_s", "unit": "elements/s", "scaling": "strong",
+            "value": total_elements / (ms_step * 1e-3), "ms_per_step": ms_step, "steps": steps,
+            "config": {"workload": f"c5: {cfg.description}", "total_elements": total_elements, "elements_per_gpu": part.max_count,
+                       "basis": [list(b) for b in cfg.basis], "rule": [list(r) for r in cfg.rules],
+                       "step": "per rank: L2 right-hand sides + fused mass-matrix assembly and solve (ib200_l2_project_mapped_batch) + "
+                               "b.u norm of its block of the 16M quads; then NCCL all-gather of the [E,25] primal DoFs to every rank and "
+                               "all-reduce of the norms, issued through the C ABI, all inside the CUDA-event region",
+                       "pipeline": f"{n_sub} sub-slabs per rank; the all-gather of sub-slab k runs on the communicator's stream "
+                                   "while sub-slab k+1 is computed",
+                       "parallelism": f"element block partition x{world}, NCCL {nccl} all-gather + all-reduce"},
+            "compute_only_ms": ms_compute, "collective_only_ms": ms_coll, "exposed_collective_ms": ms_step - ms_compute,
+            "collective": {"allgather_bytes_received_per_gpu": gather_bytes_in,
+                           "allgather_gbs_per_gpu": (gather_bytes_in / (ms_coll * 1e-3) / 1e9) if ms_coll > 0 and world > 1 else None,
+                           "link_peak_gbs_per_direction": 900.0,
+                           "link_bound_ms": gather_bytes_in / 900e9 * 1e3},
+            "single_gpu_ms": ms_single, "speedup_vs_single_gpu": ms_single / ms_step,
+            "efficiency": ms_single / ms_step / world,
+            "compute_efficiency": ms_single / ms_compute / world,
+            "collective_parity": parity, "projection_norm_sq": proj_sq, "gpu_launches": int(launches) * world,
+        }
+        return rec
+
+
+def ctx_copy_h2d(ctx, dptr: int, host: np.ndarray) -> None:
+    import ctypes as C
+
+    from interplib_b200._lib import check, lib
+
+    host = np.ascontiguousarray(host)
+    check(lib.ib200_copy_h2d(ctx.handle, C.c_void_p(dptr), host.ctypes.data_as(C.c_void_p), host.nbytes))
 
 
 # ------------------------------------------------------------------------------------------------ main
@@ -395,151 +650,47 @@ def main() -> int:
     ap.add_argument("--workload", default="c2", choices=sorted(syn.CONFIGS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--elements", type=int, default=0, help="elements per rank (default: the configuration's)")
+    ap.add_argument("--strong-elements", type=int, default=1 << 24, help="total elements of the strong-scaling record")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-mass", action="store_true", help="skip the config-5 `mass` record of the default run")
+    ap.add_argument("--no-strong", action="store_true", help="skip the config-5 strong-scaling record of the default run")
     ap.add_argument("--e2e-steps", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        return run_reference_arm(args, rank, world)
+        return run_reference_arm(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
 
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_mod
-
-        torch.cuda.set_device(local_rank)
-        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        dist = dist_mod
-
-    import interplib_b200 as ib
-
-    numa = bind_to_gpu_numa_node(local_rank)
-    ctx = ib.Context(local_rank)
-    info = ctx.info()
-    wl = Workload(args.workload, ctx, rank, args.elements or None)
-    hbm_peak, peak_src = peaks()
-
-    def barrier():
-        ctx.synchronize()
-        if dist is not None:
-            import torch
-
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        import torch
-
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---- device-resident timing -------------------------------------------------------------------------
-    for _ in range(args.warmup):
-        wl.step_device()
-    barrier()
-    sampler = ClockSampler()
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.25)
-    barrier()
-    # the W warm-up steps of a short step (C2: 0.3 ms) end long before the SM clocks have come up from idle, and the
-    # sampler's start-up pause lets them fall again: keep stepping, untimed, until the GPU has been busy for 0.2 s
-    t_warm, warm_run = time.perf_counter(), args.warmup
-    while time.perf_counter() - t_warm < 0.2:
-        for _ in range(8):
-            wl.step_device()
-        ctx.synchronize()
-        warm_run += 8
-    launches0 = ctx.stats()["kernel_launches"]
-    barrier()
-    ctx.timer_start(0)
-    for _ in range(args.steps):
-        wl.step_device()
-    ctx.timer_stop(0)
-    barrier()
-    ms_total = max_over_ranks(ctx.timer_ms(0))
-    launches = ctx.stats()["kernel_launches"] - launches0
-    clocks = sampler.stop(set(range(world))) if rank == 0 else None
-    ms_step = ms_total / args.steps
-    value = wl.E * world / (ms_step * 1e-3)
-
-    # average launch duration of the dominant kernel alone: CUDA events on the launching stream around back-to-back
-    # launches of that kernel (its output is larger than L2, so consecutive launches do not hit in cache)
-    n_dom = max(3, min(args.steps, 10))
-    launches_before = ctx.stats()["kernel_launches"]
-    ctx.timer_start(1)
-    for _ in range(n_dom):
-        wl.step_device(dominant_only=True)
-    ctx.timer_stop(1)
-    dom_launches = ctx.stats()["kernel_launches"] - launches_before
-    kernel_ms = ctx.timer_ms(1) / max(dom_launches, 1)
-    # a device-resident call larger than the context's scratch bound runs as several launches (C5: 1 863 680 elements each)
-    el_per_launch = wl.E * n_dom / max(dom_launches, 1)
-    achieved = wl.dominant_bytes_per_elem * el_per_launch / (kernel_ms * 1e-3) / 1e9
-    traffic = NCU_TRAFFIC_BYTES.get(args.workload)
-    if traffic is not None:
-        traffic = int(round(traffic[0] * (el_per_launch / traffic[1])))
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": wl.dominant,
-                "algorithmic_bytes_per_element": wl.dominant_bytes_per_elem, "step_algorithmic_bytes_per_element": wl.bytes_per_elem,
-                "step_frac": wl.bytes_per_elem * wl.E / (ms_step * 1e-3) / 1e9 / hbm_peak,
-                "elements_per_launch": el_per_launch, "kernel_ms": kernel_ms,
-                "fp64_flops_per_element": getattr(wl, "flops_per_elem", None)}
-
-    # ---- end to end through the host-pointer API (pinned host buffers) -----------------------------------------
-    e2e = None
-    if not args.no_e2e:
-        wl.e2e_prepare()
-        n_e2e = args.e2e_steps or max(3, min(args.steps, 10))
-        wl.step_e2e()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(n_e2e):
-            wl.step_e2e()
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": wl.E2 * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes,
-               "d2h_bytes_per_step": wl.d2h_bytes, "steps": n_e2e, "ms_per_step": 1e3 * dt / n_e2e,
-               "elements_per_step": wl.E2,
-               "timing": "host wall clock around the synchronous C-ABI call, max over ranks", "cpu_affinity": numa}
-
-    # ---- CPU baseline beside it (rank 0, N=1 only) -----------------------------------------------------------------
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        arm = CpuArm(args.workload, single_thread=True)
-        count = arm.calibrate(12.0)
-        t = arm.run(count, seed=7)
-        arm.close()
-        cpu = {"value": count / t, "unit": wl.unit, "cores": arm.cores, "kind": arm.kind,
-               "sample": f"{count} elements of {args.workload} in {t:.1f} s, per-element calls, single thread (the reference "
-                         "holds the GIL and has no parallel region)"}
-
-    if rank == 0:
-        cfg = wl.cfg
+    r = Runner(args)
+    name = args.workload
+    head = r.measure(name, args.steps, args.warmup, args.elements or None, sample_clocks=True, chain_e2e=name in ("c5", "c4", "c1"))
+    mass = strong = None
+    if name == "c2":
+        if not args.no_mass:
+            mass = r.measure("c5", max(5, min(args.steps, 20)), 3, None, sample_clocks=False, chain_e2e=True)
+        if not args.no_strong:
+            strong = r.measure_strong(args.strong_elements, max(5, min(args.steps, 10)), 3)
+    if r.rank == 0:
         line = {
-            "metric": wl.metric, "value": value, "unit": wl.unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": f"{cfg.name}: {cfg.description}", "elements_per_gpu": wl.E, "basis": [list(b) for b in cfg.basis],
-                       "rule": [list(r) for r in cfg.rules], "l2": "inputs+outputs larger than L2 "
-                       f"({(wl.bytes_per_elem * wl.E) >> 20} MiB per step vs 126 MB L2)", "device": info["name"],
-                       "sm_count": info["sm_count"], "parallelism": f"element-partitioned x{world}, no data-path collective",
-                       "warmup_steps_run": warm_run},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world, "clocks": clocks,
+            "metric": head["metric"], "value": head["value"], "unit": head["unit"], "n_gpus": r.world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": head["config"], "roofline": head["roofline"],
+            "cpu_baseline": head["cpu_baseline"], "e2e": head["e2e"],
+            "gpu_launches": head["gpu_launches"] + (mass["gpu_launches"] if mass else 0) + (strong["gpu_launches"] if strong else 0),
+            "clocks": head["clocks"], "run": head["run"],
         }
+        if "e2e_full_outputs" in head:
+            line["e2e_full_outputs"] = head["e2e_full_outputs"]
+        if mass is not None:
+            line["mass"] = {k: v for k, v in mass.items() if k != "clocks"}
+        if strong is not None:
+            line["strong"] = strong
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
-    ctx.close()
+    if r.dist is not None:
+        r.dist.barrier()
+        r.dist.destroy_process_group()
+    r.ctx.close()
     return 0
 
 

@@ -59,6 +59,7 @@ typedef enum
     IB200_ERROR_NO_DEVICE = 101,   /* no usable sm_100 device / context not created      */
     IB200_ERROR_BAD_ARGUMENT = 102,/* NULL pointer, dimension or index out of range      */
     IB200_ERROR_UNSUPPORTED = 103, /* valid request outside the implemented envelope     */
+    IB200_ERROR_NCCL = 104,        /* an NCCL call failed or libnccl could not be loaded */
 } interp_result_t;
 
 /* src/basis/basis_set.h:11-20 */
@@ -153,6 +154,10 @@ IB200_API int ib200_device_count(int *count);
  * src/basis/basis_set.c:212-287) and scratch.  Thread-safe (internal mutex). */
 IB200_API int ib200_ctx_create(int device, ib200_ctx_t **out);
 IB200_API int ib200_ctx_destroy(ib200_ctx_t *ctx);
+/* Waits for the context stream.  Also reports what the kernels queued by IB200_DEVICE calls found since the last
+ * synchronize: INTERP_ERROR_BAD_SYSTEM when a batched solve met a system it could not factorise (singular, indefinite
+ * or non-finite -- np.linalg.solve raises LinAlgError there, python/interplib/integration.py:221).  IB200_HOST calls
+ * report the same condition from the call itself. */
 IB200_API int ib200_ctx_synchronize(ib200_ctx_t *ctx);
 /* adopt an external cudaStream_t (e.g. torch's current stream); NULL restores the own stream */
 IB200_API int ib200_ctx_set_stream(ib200_ctx_t *ctx, void *cuda_stream);
@@ -338,6 +343,43 @@ IB200_API int ib200_l2_project_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, con
  * a = f*f and b = W*det) -- which the ranks then all-reduce (NCCL).  The reference computes such sums with
  * np.sum on the host (python/interplib/integration.py:96-103, domains.py:117). */
 IB200_API int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const double *b, double *out, int where);
+
+/* ---- 8(e): collectives over the element partition (NCCL over NVLink / NVSwitch) ------------------------------------ */
+/* The reference is single process and has no communication layer; the element-partitioned path
+ * needs two collectives and nothing else: the all-gather of per-rank [E_g][N] DoF / right-hand-side slabs and the
+ * all-reduce(sum) of a few FP64 norms.  One communicator per context (= per GPU, one process per GPU or several
+ * contexts in one process); libnccl.so.2 is loaded with dlopen at the first call (the library has no link-time
+ * dependency on NCCL), $INTERP_B200_NCCL overrides the path.  All calls are queued on the context stream unless stated
+ * otherwise; nothing synchronises with the host.  NCCL failures, including asynchronous ones
+ * (ncclCommGetAsyncError), come back as IB200_ERROR_NCCL with the text in ib200_last_error(). */
+typedef struct ib200_comm ib200_comm_t;
+enum
+{
+    IB200_COMM_ID_BYTES = 128 /* ncclUniqueId */
+};
+/* rank 0 creates the id and hands the 128 bytes to the other ranks by any means (file, socket, torch.distributed ...) */
+IB200_API int ib200_comm_unique_id(void *id);
+/* collective over all ranks of the new communicator; ctx's device is the rank's GPU */
+IB200_API int ib200_comm_create(ib200_ctx_t *ctx, int n_ranks, int rank, const void *id, ib200_comm_t **out);
+IB200_API int ib200_comm_destroy(ib200_comm_t *comm);
+IB200_API int ib200_comm_info(ib200_comm_t *comm, int *n_ranks, int *rank, int *nccl_version);
+/* ncclCommGetAsyncError: INTERP_SUCCESS while the communicator is healthy */
+IB200_API int ib200_comm_check(ib200_comm_t *comm);
+/* Block partition of the leading element index: rank g owns [g*ceil(E/G), min(E, (g+1)*ceil(E/G))). */
+IB200_API int ib200_partition_range(size_t n_elements, int n_ranks, int rank, size_t *first, size_t *count);
+/* All-gather of per-rank slabs: local[count_of_this_rank][elem_doubles] -> out[n_elements][elem_doubles] on every rank
+ * (device pointers; `local` may alias its own place inside `out`).  Uneven tails need no padding. */
+IB200_API int ib200_allgather_slabs(ib200_comm_t *comm, const double *local, size_t n_elements, size_t elem_doubles,
+                                    double *out);
+/* General form: rank r contributes counts[r] doubles which land at out + offsets[r] on every rank (counts / offsets are
+ * host arrays of n_ranks entries, identical on all ranks).  `on_side_stream` != 0 runs the collective on the
+ * communicator's own stream, ordered after the work already queued on the context stream, so that kernels queued
+ * afterwards overlap the transfer; ib200_comm_join makes the context stream wait for everything sent that way. */
+IB200_API int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *out, const size_t *counts,
+                               const size_t *offsets, int on_side_stream);
+IB200_API int ib200_comm_join(ib200_comm_t *comm);
+/* in-place all-reduce(sum) of n doubles in device memory (projection norms) */
+IB200_API int ib200_allreduce_sums(ib200_comm_t *comm, double *values, size_t n);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,7 @@ HOST, DEVICE = 0, 1
 
 # error codes that map to ValueError / MemoryError like the reference extension does
 _VALUE_ERRORS = {5, 102}
+COMM_ID_BYTES = 128
 _MEMORY_ERRORS = {3}
 
 _dp = C.POINTER(C.c_double)
@@ -174,6 +175,16 @@ _PROTOTYPES = {
     ),
     "ib200_spd_solve_batch": (C.c_int, [C.c_void_p, C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]),
     "ib200_dot": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "ib200_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "ib200_comm_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "ib200_comm_destroy": (C.c_int, [C.c_void_p]),
+    "ib200_comm_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "ib200_comm_check": (C.c_int, [C.c_void_p]),
+    "ib200_partition_range": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "ib200_allgather_slabs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]),
+    "ib200_allgatherv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.c_int]),
+    "ib200_comm_join": (C.c_int, [C.c_void_p]),
+    "ib200_allreduce_sums": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
 }
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

@@ -31,6 +31,22 @@ def _as_in(a, shape) -> np.ndarray:
     return a.reshape(shape)
 
 
+def _as_out(out, shape, name="out") -> np.ndarray:
+    """A fresh output array, or the caller's after the checks the reference applies to its ``out=`` arguments
+    (``check_input_array`` with NPY_DOUBLE / C_CONTIGUOUS / ALIGNED, e.g. src/python/degrees_of_freedom.c:377): the C
+    side writes ``prod(shape)`` doubles through the raw pointer, so anything else would corrupt the caller's heap."""
+    shape = tuple(int(v) for v in shape)
+    if out is None:
+        return np.empty(shape)
+    if not isinstance(out, np.ndarray):
+        raise TypeError(f"{name} must be a NumPy array (or a device pointer with where=DEVICE), got {type(out).__name__}")
+    if out.dtype != np.float64 or not out.flags.c_contiguous or not out.flags.writeable or not out.flags.aligned:
+        raise ValueError(f"{name} must be a writeable, aligned, C-contiguous float64 array")
+    if out.size != int(np.prod(shape, dtype=np.int64)):
+        raise ValueError(f"{name} must hold {int(np.prod(shape, dtype=np.int64))} values (shape {shape}), it holds {out.size}")
+    return out
+
+
 def _ptr(a):
     if a is None:
         return None
@@ -163,8 +179,7 @@ class Context:
         if where == HOST:
             dofs = _as_in(dofs, (-1, N))
             E = dofs.shape[0]
-            if out is None:
-                out = np.empty((E, len(deriv_masks), Q))
+            out = _as_out(out, (E, len(deriv_masks), Q))
         else:
             E = int(n_elements)
         check(lib.ib200_reconstruct_batch(self.handle, len(basis), basis_specs(basis), rule_specs(rules), E, _ptr(dofs),
@@ -179,8 +194,7 @@ class Context:
             x = np.ascontiguousarray(x, dtype=np.float64)
             assert x.ndim == 3 and x.shape[1] == ndim, "x must be [E][ndim][P]"
             E, P = x.shape[0], x.shape[2]
-            if out is None:
-                out = np.empty((E, P, N))
+            out = _as_out(out, (E, P, N))
         else:
             E, P = int(n_elements), int(n_points)
         check(lib.ib200_evaluate_points_batch(self.handle, ndim, basis_specs(basis), E, P, _ptr(x), _ptr(out), where))
@@ -196,8 +210,7 @@ class Context:
             x = np.ascontiguousarray(x, dtype=np.float64)
             assert x.ndim == 3 and x.shape[0] == E and x.shape[1] == ndim, "x must be [E][ndim][P]"
             P = x.shape[2]
-            if out is None:
-                out = np.empty((E, len(deriv_masks), P))
+            out = _as_out(out, (E, len(deriv_masks), P))
         else:
             E, P = int(n_elements), int(n_points)
         check(lib.ib200_reconstruct_points_batch(self.handle, ndim, basis_specs(basis), E, _ptr(dofs), P, _ptr(x),
@@ -212,8 +225,7 @@ class Context:
         if where == HOST:
             dofs = _as_in(dofs, (-1, N))
             E = dofs.shape[0]
-            if out is None:
-                out = np.empty((E, _n_basis(lower) if 0 <= idim < len(basis) and basis[idim][1] > 0 else 0))
+            out = _as_out(out, (E, _n_basis(lower) if 0 <= idim < len(basis) and basis[idim][1] > 0 else 0))
         else:
             E = int(n_elements)
         check(lib.ib200_dof_derivative_batch(self.handle, len(basis), basis_specs(basis), int(idim), E, _ptr(dofs), _ptr(out),
@@ -228,9 +240,9 @@ class Context:
         if where == HOST:
             geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
             E = geom_dofs.shape[0]
-            coords = np.empty((E, n_phys, 1 + d, Q)) if "coords" in want else None
-            det = np.empty((E, Q)) if "det" in want else None
-            jinv = np.empty((E, Q, d, n_phys)) if "jinv" in want else None
+            coords = _as_out(coords, (E, n_phys, 1 + d, Q), "coords") if "coords" in want else None
+            det = _as_out(det, (E, Q), "det") if "det" in want else None
+            jinv = _as_out(jinv, (E, Q, d, n_phys), "jinv") if "jinv" in want else None
         else:
             E = int(n_elements)
         check(lib.ib200_geometry_batch(self.handle, d, n_phys, basis_specs(geom_basis), rule_specs(rules), E,
@@ -245,8 +257,7 @@ class Context:
         if where == HOST:
             if weight is not None:
                 weight = _as_in(weight, (E, Q))
-            if out is None:
-                out = np.empty((E, Nout, Nin))
+            out = _as_out(out, (E, Nout, Nin))
         check(lib.ib200_mass_matrix_batch(self.handle, len(rules), basis_specs(basis_in), basis_specs(basis_out),
                                           rule_specs(rules), E, _ptr(weight), int(deriv_dim_in), _ptr(out), where))
         return out
@@ -258,8 +269,7 @@ class Context:
         if where == HOST:
             geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
             E = geom_dofs.shape[0]
-            if out is None:
-                out = np.empty((E, Nout, Nin))
+            out = _as_out(out, (E, Nout, Nin))
         else:
             E = int(n_elements)
         check(lib.ib200_mass_matrix_mapped_batch(self.handle, len(rules), basis_specs(basis_in), basis_specs(basis_out),
@@ -276,8 +286,7 @@ class Context:
             E = fvals.shape[0]
             if det is not None:
                 det = _as_in(det, (E, Q))
-            if out is None:
-                out = np.empty((E, N))
+            out = _as_out(out, (E, N))
         else:
             E = int(n_elements)
         check(lib.ib200_l2_dual_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), E, _ptr(fvals),
@@ -291,8 +300,7 @@ class Context:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
             geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
-            if out is None:
-                out = np.empty((E, N))
+            out = _as_out(out, (E, N))
         else:
             E = int(n_elements)
         check(lib.ib200_l2_dual_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
@@ -307,10 +315,8 @@ class Context:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
             geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
-            if mass is None:
-                mass = np.empty((E, N, N))
-            if rhs is None:
-                rhs = np.empty((E, N))
+            mass = _as_out(mass, (E, N, N), "mass")
+            rhs = _as_out(rhs, (E, N), "rhs")
         else:
             E = int(n_elements)
         check(lib.ib200_l2_system_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,
@@ -327,8 +333,7 @@ class Context:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
             geom_dofs = _as_in(geom_dofs, (E, n_phys, Ng))
-            if out is None:
-                out = np.empty((E, N))
+            out = _as_out(out, (E, N))
         else:
             E = int(n_elements)
         check(lib.ib200_l2_project_mapped_batch(self.handle, len(rules), basis_specs(basis), rule_specs(rules), n_phys,

@@ -6,7 +6,18 @@
 #include <string>
 #include <thread>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "ctx.cuh"
+
+NvtxRange::NvtxRange(const char *name)
+{
+    nvtxRangePushA(name);
+}
+NvtxRange::~NvtxRange()
+{
+    nvtxRangePop();
+}
 
 // ---- errors -----------------------------------------------------------------------------------------
 static thread_local std::string g_last_error;
@@ -53,6 +64,7 @@ extern "C" const char *ib200_error_str(int code)
     case IB200_ERROR_NO_DEVICE: return "IB200_ERROR_NO_DEVICE";
     case IB200_ERROR_BAD_ARGUMENT: return "IB200_ERROR_BAD_ARGUMENT";
     case IB200_ERROR_UNSUPPORTED: return "IB200_ERROR_UNSUPPORTED";
+    case IB200_ERROR_NCCL: return "IB200_ERROR_NCCL";
     default: return "Unknown";
     }
 }
@@ -77,6 +89,7 @@ extern "C" const char *ib200_error_msg(int code)
     case IB200_ERROR_NO_DEVICE: return "No usable CUDA device (the batched path has no CPU fallback)";
     case IB200_ERROR_BAD_ARGUMENT: return "Bad argument";
     case IB200_ERROR_UNSUPPORTED: return "Request is outside the implemented envelope";
+    case IB200_ERROR_NCCL: return "An NCCL call failed or libnccl could not be loaded";
     default: return "Unknown error";
     }
 }
@@ -234,6 +247,9 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
             IB_CUDA(cudaEventCreate(&ctx->timer[i][j]));
     IB_CUDA(cudaMalloc((void **)&ctx->sched_ring, sizeof(unsigned long long) * 2 * ib200_ctx::kSchedRing));
     IB_CUDA(cudaMemset(ctx->sched_ring, 0, sizeof(unsigned long long) * 2 * ib200_ctx::kSchedRing));
+    IB_CUDA(cudaHostAlloc((void **)&ctx->status_host, sizeof(int), cudaHostAllocMapped));
+    *ctx->status_host = 0;
+    IB_CUDA(cudaHostGetDevicePointer((void **)&ctx->status_dev, ctx->status_host, 0));
     *out = ctx;
     return INTERP_SUCCESS;
 }
@@ -286,6 +302,7 @@ extern "C" int ib200_ctx_destroy(ib200_ctx_t *ctx)
     cudaFree(ctx->scratch);
     cudaFree(ctx->dot_partial);
     cudaFree(ctx->sched_ring);
+    cudaFreeHost(ctx->status_host);
     for (int i = 0; i < 8; ++i)
         for (int j = 0; j < 2; ++j)
             cudaEventDestroy(ctx->timer[i][j]);
@@ -294,11 +311,19 @@ extern "C" int ib200_ctx_destroy(ib200_ctx_t *ctx)
     return INTERP_SUCCESS;
 }
 
+int ctx_take_status(ib200_ctx *ctx)
+{
+    const int st = __atomic_exchange_n(ctx->status_host, 0, __ATOMIC_ACQ_REL);
+    if (st & IB200_STATUS_BAD_SYSTEM)
+        return ib200_fail(INTERP_ERROR_BAD_SYSTEM, "a batched solve met a matrix that is singular, indefinite or not finite");
+    return INTERP_SUCCESS;
+}
+
 extern "C" int ib200_ctx_synchronize(ib200_ctx_t *ctx)
 {
     IB_TRY(ctx_check(ctx));
     IB_CUDA(cudaStreamSynchronize(ctx->stream));
-    return INTERP_SUCCESS;
+    return ctx_take_status(ctx);
 }
 
 extern "C" int ib200_ctx_set_stream(ib200_ctx_t *ctx, void *cuda_stream)
@@ -595,11 +620,12 @@ struct BatchArray
 // PCIe then carries, so slabs of 2 MB and more are split over a few threads (IB200_STAGE_THREADS, default 4, 1 = off).
 void stage_memcpy(void *dst, const void *src, size_t bytes)
 {
+    constexpr int kMaxParts = 16; // the caller + 15 workers
     static const int n_threads = [] {
         const char *env = getenv("IB200_STAGE_THREADS");
         const int want = env ? atoi(env) : 4;
         const int hw = (int)std::thread::hardware_concurrency();
-        return std::max(1, std::min(want, hw > 1 ? hw / 2 : 1));
+        return std::max(1, std::min({want, hw > 1 ? hw / 2 : 1, kMaxParts}));
     }();
     if (n_threads == 1 || bytes < ((size_t)2 << 20))
     {
@@ -607,10 +633,19 @@ void stage_memcpy(void *dst, const void *src, size_t bytes)
         return;
     }
     const size_t part = ((bytes / n_threads) + 4095) & ~(size_t)4095;
-    std::thread workers[16];
+    std::thread workers[kMaxParts - 1];
     int n = 0;
-    for (size_t off = part; off < bytes && n < 15; off += part, ++n)
-        workers[n] = std::thread([=] { std::memcpy((char *)dst + off, (const char *)src + off, std::min(part, bytes - off)); });
+    for (size_t off = part; off < bytes; off += part, ++n)
+    {
+        // the last worker takes whatever is left, so the parts always cover [0, bytes)
+        const size_t len = (n == kMaxParts - 2) ? bytes - off : std::min(part, bytes - off);
+        workers[n] = std::thread([=] { std::memcpy((char *)dst + off, (const char *)src + off, len); });
+        if (n == kMaxParts - 2)
+        {
+            ++n;
+            break;
+        }
+    }
     std::memcpy(dst, src, std::min(part, bytes));
     for (int i = 0; i < n; ++i)
         workers[i].join();
@@ -672,9 +707,13 @@ template <class Launch>
 int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int where, size_t max_device_chunk, Launch launch)
 {
     const int n_arr = (int)arrays.size();
+    if (where != IB200_HOST && where != IB200_DEVICE)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
+    if (E == 0)
+        return INTERP_SUCCESS; // an empty batch launches nothing, on either path
     if (where == IB200_DEVICE)
     {
-        LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
+        LaunchCfg cfg = make_launch_cfg(ctx, ctx->stream);
         // scratch arrays come from the context; bound them by running sub-chunks
         size_t scratch_per_elem = 0;
         for (auto &a : arrays)
@@ -700,7 +739,7 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
             scratch = (char *)p;
         }
         std::vector<void *> dev(n_arr);
-        for (size_t first = 0; first < E || (E == 0 && first == 0); first += std::max<size_t>(chunk, 1))
+        for (size_t first = 0; first < E; first += chunk)
         {
             const size_t cnt = std::min(chunk, E - first);
             size_t off = 0;
@@ -717,15 +756,9 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
                 }
             }
             IB_TRY(launch(cfg, first, cnt, dev.data()));
-            if (E == 0)
-                break;
         }
         return INTERP_SUCCESS;
     }
-    if (where != IB200_HOST)
-        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
-    if (E == 0)
-        return INTERP_SUCCESS;
 
     // ---- host pointers: three slots, each with its own stream, device slab and pinned slab -----------------
     size_t per_elem = 0, dev_per_elem = 0; // bytes that cross PCIe / bytes of the device slab (scratch included)
@@ -791,11 +824,10 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
         return INTERP_SUCCESS;
     };
 
+    // one chunk: stage in, launch, stage out.  Any failure leaves earlier chunks' asynchronous copies into the caller's
+    // arrays in flight, so the error path below waits for them before the call returns.
     std::vector<void *> dev(n_arr);
-    int slot = 0;
-    for (size_t first = 0; first < E; first += chunk, slot = (slot + 1) % n_slots)
-    {
-        const size_t cnt = std::min(chunk, E - first);
+    auto submit = [&](int slot, size_t first, size_t cnt) -> int {
         IB_TRY(drain(slot));
         cudaStream_t st = ctx->io_stream[slot];
         for (int i = 0; i < n_arr; ++i)
@@ -812,7 +844,7 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
             }
             IB_CUDA(cudaMemcpyAsync(dev[i], src, cnt * a.elem_bytes, cudaMemcpyHostToDevice, st));
         }
-        LaunchCfg cfg{st, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
+        LaunchCfg cfg = make_launch_cfg(ctx, st);
         IB_TRY(launch(cfg, first, cnt, dev.data()));
         for (int i = 0; i < n_arr; ++i)
         {
@@ -826,10 +858,24 @@ int run_batched(ib200_ctx *ctx, size_t E, std::vector<BatchArray> arrays, int wh
         pending[slot].busy = true;
         pending[slot].first = first;
         pending[slot].cnt = cnt;
+        return INTERP_SUCCESS;
+    };
+    int res = INTERP_SUCCESS, slot = 0;
+    for (size_t first = 0; first < E && res == INTERP_SUCCESS; first += chunk, slot = (slot + 1) % n_slots)
+        res = submit(slot, first, std::min(chunk, E - first));
+    if (res != INTERP_SUCCESS)
+    {
+        // keep the first error's text; nothing may still be writing into caller memory when we return
+        const std::string first_error = g_last_error;
+        for (int s = 0; s < n_slots; ++s)
+            cudaStreamSynchronize(ctx->io_stream[s]);
+        cudaGetLastError();
+        g_last_error = first_error;
+        return res;
     }
     for (int s = 0; s < n_slots; ++s)
         IB_TRY(drain(s));
-    return INTERP_SUCCESS;
+    return ctx_take_status(ctx); // everything this call queued has completed
 }
 
 bool spaces_match(unsigned ndim, const basis_spec_t *a, const basis_spec_t *b)
@@ -867,6 +913,7 @@ extern "C" int ib200_reconstruct_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_reconstruct_batch");
     if (!deriv_masks || n_fields == 0 || n_fields > 8)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..8 fields and their derivative masks");
     if (n_elements && (!dofs || !out))
@@ -939,6 +986,7 @@ extern "C" int ib200_evaluate_points_batch(ib200_ctx_t *ctx, unsigned ndim, cons
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_evaluate_points_batch");
     if (n_elements && n_points && (!x || !out))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "x/out must not be NULL");
     PointOp op;
@@ -958,6 +1006,7 @@ extern "C" int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, c
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_reconstruct_points_batch");
     if (!deriv_masks || n_fields == 0 || n_fields > 8)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..8 fields and their derivative masks");
     if (n_elements && n_points && (!dofs || !x || !out))
@@ -998,6 +1047,7 @@ extern "C" int ib200_dof_derivative_batch(ib200_ctx_t *ctx, unsigned ndim, const
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_dof_derivative_batch");
     if (ndim == 0 || ndim > IB200_MAX_DIM || !basis)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "need 1..%d dimensions", (int)IB200_MAX_DIM);
     if (idim >= ndim)
@@ -1056,6 +1106,7 @@ extern "C" int ib200_geometry_batch(ib200_ctx_t *ctx, unsigned ndim, unsigned n_
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_geometry_batch");
     IB_TRY(check_geometry_dims(ndim, n_phys));
     if (n_elements && !geom_dofs)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs must not be NULL");
@@ -1103,6 +1154,7 @@ extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_mass_matrix_batch");
     if (!basis_in || !basis_out)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis_in/basis_out must not be NULL");
     if (n_elements && !out)
@@ -1140,6 +1192,7 @@ extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, c
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_mass_matrix_mapped_batch");
     IB_TRY(check_geometry_dims(ndim, n_phys));
     if (!basis_in || !basis_out || !geom_basis)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis_in/basis_out/geom_basis must not be NULL");
@@ -1194,6 +1247,7 @@ extern "C" int ib200_l2_dual_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_l2_dual_batch");
     if (n_elements && (!fvals || !out))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "fvals/out must not be NULL");
     OpDesc op;
@@ -1224,6 +1278,7 @@ extern "C" int ib200_l2_dual_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_l2_dual_mapped_batch");
     IB_TRY(check_geometry_dims(ndim, n_phys));
     if (n_elements && (!fvals || !out || !geom_dofs))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/fvals/out must not be NULL");
@@ -1270,6 +1325,7 @@ static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *b
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx(solve ? "ib200_l2_project_mapped_batch" : "ib200_l2_system_mapped_batch");
     IB_TRY(check_geometry_dims(ndim, n_phys));
     if (!basis || !geom_basis)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/geom_basis must not be NULL");
@@ -1351,6 +1407,7 @@ extern "C" int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elem
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_spd_solve_batch");
     if (n_elements && (!mass || !rhs))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "mass/rhs must not be NULL");
     if (n == 0 || n > 4096)
@@ -1368,11 +1425,12 @@ extern "C" int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const doub
 {
     IB_TRY(ctx_check(ctx));
     std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_dot");
     if (!out || (n && (!a || !b)))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "a/b/out must not be NULL");
     if (where != IB200_DEVICE && where != IB200_HOST)
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "`where` must be IB200_HOST or IB200_DEVICE");
-    LaunchCfg cfg{ctx->stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched()};
+    LaunchCfg cfg = make_launch_cfg(ctx, ctx->stream);
     if (!ctx->dot_partial)
         IB_CUDA(cudaMalloc((void **)&ctx->dot_partial, sizeof(double) * (dot_scratch_doubles() + 1)));
     double *partial = ctx->dot_partial;

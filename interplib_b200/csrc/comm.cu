@@ -1,0 +1,325 @@
+// the two collectives of the element-partitioned path behind the C ABI -- all-gather of per-rank DoF /
+// right-hand-side slabs and all-reduce(sum) of projection norms -- over NCCL (NVLink 5 / NVSwitch on one box).
+// The reference has no communication layer (single process, /root/reference has no MPI/NCCL call site); this file is
+// new.  NCCL is bound at run time with dlopen so that libinterp_b200.so loads on hosts without it and shares the
+// libnccl.so.2 a host framework (torch) may already have mapped.
+#include <dlfcn.h>
+#include <nccl.h> // types and enums only: every function is resolved with dlsym
+
+#include <cstdlib>
+#include <mutex>
+#include <vector>
+
+#include "ctx.cuh"
+
+namespace
+{
+
+struct NcclApi
+{
+    void *handle = nullptr;
+    ncclResult_t (*GetVersion)(int *) = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommGetAsyncError)(ncclComm_t, ncclResult_t *) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    const char *(*GetLastError)(ncclComm_t) = nullptr;
+};
+
+NcclApi g_nccl;
+std::once_flag g_nccl_once;
+std::string g_nccl_load_error;
+
+void load_nccl()
+{
+    const char *env = std::getenv("INTERP_B200_NCCL");
+    const char *names[] = {env, "libnccl.so.2", "libnccl.so"};
+    for (const char *name : names)
+    {
+        if (!name || !*name)
+            continue;
+        g_nccl.handle = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.handle)
+            break;
+        g_nccl_load_error = dlerror();
+    }
+    if (!g_nccl.handle)
+        return;
+    bool ok = true;
+    auto sym = [&](const char *name, bool required = true) -> void * {
+        void *p = dlsym(g_nccl.handle, name);
+        if (!p && required)
+        {
+            ok = false;
+            g_nccl_load_error = std::string("symbol ") + name + " missing from libnccl";
+        }
+        return p;
+    };
+#define IB_SYM(field, name) g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(sym(name))
+    IB_SYM(GetVersion, "ncclGetVersion");
+    IB_SYM(GetUniqueId, "ncclGetUniqueId");
+    IB_SYM(CommInitRank, "ncclCommInitRank");
+    IB_SYM(CommDestroy, "ncclCommDestroy");
+    IB_SYM(CommAbort, "ncclCommAbort");
+    IB_SYM(CommGetAsyncError, "ncclCommGetAsyncError");
+    IB_SYM(AllGather, "ncclAllGather");
+    IB_SYM(AllReduce, "ncclAllReduce");
+    IB_SYM(Broadcast, "ncclBroadcast");
+    IB_SYM(GroupStart, "ncclGroupStart");
+    IB_SYM(GroupEnd, "ncclGroupEnd");
+    IB_SYM(GetErrorString, "ncclGetErrorString");
+#undef IB_SYM
+    g_nccl.GetLastError = reinterpret_cast<decltype(g_nccl.GetLastError)>(sym("ncclGetLastError", false));
+    if (!ok)
+    {
+        dlclose(g_nccl.handle);
+        g_nccl.handle = nullptr;
+    }
+}
+
+int need_nccl()
+{
+    std::call_once(g_nccl_once, load_nccl);
+    if (!g_nccl.handle)
+        return ib200_fail(IB200_ERROR_NCCL, "libnccl.so.2 could not be loaded (%s); set $INTERP_B200_NCCL to its path",
+                          g_nccl_load_error.c_str());
+    return INTERP_SUCCESS;
+}
+
+} // namespace
+
+struct ib200_comm
+{
+    ib200_ctx *ctx = nullptr;
+    ncclComm_t nccl = nullptr;
+    int n_ranks = 1, rank = 0;
+    cudaStream_t side = nullptr; // stream of overlapped collectives
+    cudaEvent_t fork = nullptr, join = nullptr;
+    bool side_busy = false;
+};
+
+namespace
+{
+
+int nccl_fail(ib200_comm *comm, ncclResult_t res, const char *what)
+{
+    const char *detail = (comm && comm->nccl && g_nccl.GetLastError) ? g_nccl.GetLastError(comm->nccl) : "";
+    return ib200_fail(IB200_ERROR_NCCL, "%s failed: %s%s%s", what, g_nccl.GetErrorString(res), (detail && *detail) ? " -- " : "",
+                      detail ? detail : "");
+}
+
+#define IB_NCCL(comm, call)                             \
+    do                                                  \
+    {                                                   \
+        const ncclResult_t ib_nres__ = (call);          \
+        if (ib_nres__ != ncclSuccess)                   \
+            return nccl_fail(comm, ib_nres__, #call);   \
+    } while (0)
+
+int comm_check(ib200_comm *comm)
+{
+    if (!comm || !comm->ctx)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "communicator is NULL");
+    IB_CUDA(cudaSetDevice(comm->ctx->device));
+    return INTERP_SUCCESS;
+}
+
+} // namespace
+
+extern "C" int ib200_partition_range(size_t n_elements, int n_ranks, int rank, size_t *first, size_t *count)
+{
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks || !first || !count)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "rank %d outside a world of %d (or NULL output)", rank, n_ranks);
+    const size_t per = (n_elements + (size_t)n_ranks - 1) / (size_t)n_ranks;
+    const size_t f = std::min(n_elements, (size_t)rank * per);
+    *first = f;
+    *count = std::min(n_elements, f + per) - f;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_unique_id(void *id)
+{
+    if (!id)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "id must not be NULL");
+    IB_TRY(need_nccl());
+    static_assert(sizeof(ncclUniqueId) == IB200_COMM_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId uid;
+    IB_NCCL(nullptr, g_nccl.GetUniqueId(&uid));
+    std::memcpy(id, &uid, sizeof uid);
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_create(ib200_ctx_t *ctx, int n_ranks, int rank, const void *id, ib200_comm_t **out)
+{
+    if (!ctx)
+        return ib200_fail(IB200_ERROR_NO_DEVICE, "context is NULL (no CUDA device?)");
+    if (!out || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "bad communicator arguments (rank %d of %d)", rank, n_ranks);
+    *out = nullptr;
+    IB_TRY(need_nccl());
+    IB_CUDA(cudaSetDevice(ctx->device));
+    ib200_comm *comm = new (std::nothrow) ib200_comm;
+    if (!comm)
+        return ib200_fail(INTERP_ERROR_FAILED_ALLOCATION, "out of host memory");
+    comm->ctx = ctx;
+    comm->n_ranks = n_ranks;
+    comm->rank = rank;
+    ncclUniqueId uid;
+    std::memcpy(&uid, id, sizeof uid);
+    const ncclResult_t res = g_nccl.CommInitRank(&comm->nccl, n_ranks, uid, rank);
+    if (res != ncclSuccess)
+    {
+        delete comm;
+        return nccl_fail(nullptr, res, "ncclCommInitRank");
+    }
+    if (cudaStreamCreateWithFlags(&comm->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&comm->fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&comm->join, cudaEventDisableTiming) != cudaSuccess)
+    {
+        ib200_comm_destroy(comm);
+        return ib200_fail(IB200_ERROR_CUDA, "could not create the communicator's stream / events");
+    }
+    *out = comm;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_destroy(ib200_comm_t *comm)
+{
+    if (!comm)
+        return INTERP_SUCCESS;
+    if (comm->ctx)
+        cudaSetDevice(comm->ctx->device);
+    if (comm->side)
+    {
+        cudaStreamSynchronize(comm->side);
+        cudaStreamDestroy(comm->side);
+    }
+    if (comm->fork)
+        cudaEventDestroy(comm->fork);
+    if (comm->join)
+        cudaEventDestroy(comm->join);
+    if (comm->nccl && g_nccl.handle)
+    {
+        if (comm->ctx)
+            cudaStreamSynchronize(comm->ctx->stream);
+        g_nccl.CommDestroy(comm->nccl);
+    }
+    delete comm;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_info(ib200_comm_t *comm, int *n_ranks, int *rank, int *nccl_version)
+{
+    IB_TRY(comm_check(comm));
+    if (n_ranks)
+        *n_ranks = comm->n_ranks;
+    if (rank)
+        *rank = comm->rank;
+    if (nccl_version)
+        IB_NCCL(comm, g_nccl.GetVersion(nccl_version));
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_check(ib200_comm_t *comm)
+{
+    IB_TRY(comm_check(comm));
+    ncclResult_t async = ncclSuccess;
+    IB_NCCL(comm, g_nccl.CommGetAsyncError(comm->nccl, &async));
+    if (async != ncclSuccess && async != ncclInProgress)
+        return nccl_fail(comm, async, "asynchronous NCCL operation");
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *out, const size_t *counts,
+                                const size_t *offsets, int on_side_stream)
+{
+    IB_TRY(comm_check(comm));
+    if (!counts || !offsets)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "counts/offsets must not be NULL");
+    size_t total = 0;
+    bool even = true, packed = true;
+    for (int r = 0; r < comm->n_ranks; ++r)
+    {
+        total += counts[r];
+        even = even && counts[r] == counts[0];
+        packed = packed && offsets[r] == (size_t)r * counts[0];
+    }
+    if (total == 0)
+        return INTERP_SUCCESS;
+    if (!out || (counts[comm->rank] && !send))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "send/out must not be NULL");
+    ib200_ctx *ctx = comm->ctx;
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    cudaStream_t st = ctx->stream;
+    if (on_side_stream)
+    {
+        IB_CUDA(cudaEventRecord(comm->fork, ctx->stream));
+        IB_CUDA(cudaStreamWaitEvent(comm->side, comm->fork, 0));
+        st = comm->side;
+        comm->side_busy = true;
+    }
+    if (even && packed)
+    {
+        // equal, back-to-back slabs: the library's all-gather (in place when `send` already sits at its offset)
+        IB_NCCL(comm, g_nccl.AllGather(send, out, counts[0], ncclDouble, comm->nccl, st));
+        return INTERP_SUCCESS;
+    }
+    // ragged or strided destinations: one broadcast per rank, fused into one NCCL group (a single launch)
+    IB_NCCL(comm, g_nccl.GroupStart());
+    ncclResult_t res = ncclSuccess;
+    for (int r = 0; r < comm->n_ranks && res == ncclSuccess; ++r)
+        if (counts[r])
+            res = g_nccl.Broadcast(r == comm->rank ? (const void *)send : (const void *)(out + offsets[r]), out + offsets[r],
+                                   counts[r], ncclDouble, r, comm->nccl, st);
+    const ncclResult_t end = g_nccl.GroupEnd();
+    if (res != ncclSuccess)
+        return nccl_fail(comm, res, "ncclBroadcast");
+    IB_NCCL(comm, end);
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_allgather_slabs(ib200_comm_t *comm, const double *local, size_t n_elements, size_t elem_doubles,
+                                     double *out)
+{
+    IB_TRY(comm_check(comm));
+    std::vector<size_t> counts(comm->n_ranks), offsets(comm->n_ranks);
+    for (int r = 0; r < comm->n_ranks; ++r)
+    {
+        size_t first, cnt;
+        IB_TRY(ib200_partition_range(n_elements, comm->n_ranks, r, &first, &cnt));
+        counts[r] = cnt * elem_doubles;
+        offsets[r] = first * elem_doubles;
+    }
+    return ib200_allgatherv(comm, local, out, counts.data(), offsets.data(), 0);
+}
+
+extern "C" int ib200_comm_join(ib200_comm_t *comm)
+{
+    IB_TRY(comm_check(comm));
+    std::lock_guard<std::mutex> lock(comm->ctx->mutex);
+    if (!comm->side_busy)
+        return INTERP_SUCCESS;
+    IB_CUDA(cudaEventRecord(comm->join, comm->side));
+    IB_CUDA(cudaStreamWaitEvent(comm->ctx->stream, comm->join, 0));
+    comm->side_busy = false;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_allreduce_sums(ib200_comm_t *comm, double *values, size_t n)
+{
+    IB_TRY(comm_check(comm));
+    if (n == 0)
+        return INTERP_SUCCESS;
+    if (!values)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "values must not be NULL");
+    std::lock_guard<std::mutex> lock(comm->ctx->mutex);
+    IB_NCCL(comm, g_nccl.AllReduce(values, values, n, ncclDouble, ncclSum, comm->nccl, comm->ctx->stream));
+    return INTERP_SUCCESS;
+}

@@ -132,6 +132,10 @@ struct ib200_ctx
     // never share one
     unsigned long long *sched_ring = nullptr;
     unsigned sched_next = 0;
+    // status word the kernels raise (bit 0: a batched solve met a system it could not factorise): pinned host memory
+    // mapped into the device, read by the host after a synchronisation without a copy
+    int *status_host = nullptr;
+    int *status_dev = nullptr;
     static constexpr unsigned kSchedRing = 256;
     unsigned long long *next_sched() { return sched_ring + 2 * (sched_next++ % kSchedRing); }
 };
@@ -152,6 +156,24 @@ struct LaunchCfg
     bool force_generic;
     unsigned long long *launch_counter;
     unsigned long long *sched; // device counter pair {next tile, finished CTAs} for dynamically scheduled kernels
+    int *status;               // device view of the context's status word (IB200_STATUS_* bits)
+};
+enum
+{
+    IB200_STATUS_BAD_SYSTEM = 1
+};
+inline LaunchCfg make_launch_cfg(ib200_ctx *ctx, cudaStream_t stream)
+{
+    return LaunchCfg{stream, ctx->prop.multiProcessorCount, ctx->force_generic, &ctx->launches, ctx->next_sched(), ctx->status_dev};
+}
+// Reads and clears the status word (call after the producing stream has been synchronised).
+int ctx_take_status(ib200_ctx *ctx);
+
+// NVTX range around every batched C-ABI call (visible in Nsight Systems / ncu --nvtx; a no-op without a tool attached).
+struct NvtxRange
+{
+    explicit NvtxRange(const char *name);
+    ~NvtxRange();
 };
 
 int launch_reconstruct_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const double *dofs, unsigned n_fields,

@@ -414,10 +414,24 @@ __global__ void __launch_bounds__(kThreads)
     }
 }
 
-// ---- N1: batched SPD solve, one warp per element, Cholesky in place in global/L2 ---------------------------
+// ---- N1: batched solve of M u = b --------------------------------------------------------------------------------
+// The reference solves with LAPACK LU (np.linalg.solve, python/interplib/integration.py:221), which does not care about
+// the sign of M: a negatively oriented element (clockwise quad corners, a line with decreasing knots) has det J < 0
+// and a NEGATIVE definite mass matrix with a perfectly good solution.  Every kernel below therefore factorises
+// sign(M[0][0]) * M and substitutes sign(M[0][0]) * b (same u), and raises IB200_STATUS_BAD_SYSTEM when the solution is
+// not finite (a non-positive pivot of the signed matrix gives rsqrt -> NaN/inf): singular and indefinite systems
+// surface as INTERP_ERROR_BAD_SYSTEM instead of silent NaNs.
+__device__ __forceinline__ void spd_flag_if_bad(double u, int *status)
+{
+    if (!(fabs(u) <= 1.79769313486231570e308)) // NaN or infinite
+        atomicOr(status, IB200_STATUS_BAD_SYSTEM);
+}
+
+// one warp per element, Cholesky in place in global/L2 (fallback for systems no other kernel takes)
 // projection_l2_primal (python/interplib/integration.py:212-221) solves M u = b per element with LAPACK LU;
 // M is SPD (cond <= ~1e3 on these spaces) so Cholesky agrees to ~1e-14.
-__global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double *__restrict__ mass, double *__restrict__ rhs)
+__global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double *__restrict__ mass, double *__restrict__ rhs,
+                                                        int *__restrict__ status)
 {
     const int lane = threadIdx.x & 31;
     const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
@@ -426,6 +440,14 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
     {
         double *A = mass + e * (size_t)n * n;
         double *b = rhs + e * (size_t)n;
+        if (A[0] < 0.0) // warp uniform: negative definite -> factorise -M, solve with -b
+        {
+            __syncwarp();
+            for (int idx = lane; idx < n * n; idx += 32)
+                A[idx] = -A[idx];
+            for (int j = lane; j < n; j += 32)
+                b[j] = -b[j];
+        }
         // right-looking Cholesky, lower triangle
         for (int k = 0; k < n; ++k)
         {
@@ -468,6 +490,8 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
                 b[i] -= A[k * n + i] * xk;
         }
         __syncwarp();
+        for (int j = lane; j < n; j += 32)
+            spd_flag_if_bad(b[j], status);
     }
 }
 
@@ -478,7 +502,7 @@ __global__ void __launch_bounds__(128) spd_solve_kernel(int n, size_t E, double 
 // s_i = A[i][k] - sum_{m<k} L[i][m] L[k][m] (its own row: stride ld, odd -> conflict-free; the pivot row: broadcast),
 // then L[i][k] = s_i * rsqrt(s_k).  Back substitution is column oriented (no reductions).
 __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size_t E, const double *__restrict__ mass,
-                                                             double *__restrict__ rhs)
+                                                             double *__restrict__ rhs, int *__restrict__ status)
 {
     extern __shared__ __align__(16) double chol_smem[];
     const int lane = threadIdx.x & 31, warp_in_cta = threadIdx.x >> 5;
@@ -490,14 +514,15 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
         const double *A = mass + e * (size_t)n * n;
         double *b = rhs + e * (size_t)n;
         __syncwarp();
+        const double sg = A[0] < 0.0 ? -1.0 : 1.0;
         for (int idx = lane, i = 0, j = lane; idx < n * n; idx += 32, j += 32)
         {
             while (j >= n)
                 j -= n, ++i;
-            L[i * ld + j] = __ldcs(A + idx);
+            L[i * ld + j] = sg * __ldcs(A + idx);
         }
         for (int j = lane; j < n; j += 32)
-            L[n * ld + j] = b[j];
+            L[n * ld + j] = sg * b[j];
         __syncwarp();
         for (int k = 0; k < n; ++k)
         {
@@ -544,7 +569,10 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
             __syncwarp();
         }
         for (int j = lane; j < n; j += 32)
+        {
             b[j] = y[j];
+            spd_flag_if_bad(y[j], status);
+        }
     }
 }
 
@@ -556,7 +584,8 @@ __global__ void __launch_bounds__(128) spd_solve_smem_kernel(int n, int ld, size
 // a[j] -= l_ik * l_jk.  The forward substitution rides along (b is one more register).  About 1/5 of the instructions of
 // the shared-memory kernel above, which spends most of its issue slots on loop control and the FP64 division routine.
 template <int N>
-__global__ void __launch_bounds__(128) spd_solve_reg_kernel(size_t E, const double *__restrict__ mass, double *__restrict__ rhs)
+__global__ void __launch_bounds__(128) spd_solve_reg_kernel(size_t E, const double *__restrict__ mass, double *__restrict__ rhs,
+                                                            int *__restrict__ status)
 {
     constexpr int LD = N | 1, PANEL = (N * LD + 1) & ~1; // doubles; panels stay 16-byte aligned
     extern __shared__ __align__(16) double chol_reg_smem[]; // [4 warps][2 panels][PANEL]
@@ -600,6 +629,13 @@ __global__ void __launch_bounds__(128) spd_solve_reg_kernel(size_t E, const doub
 #pragma unroll
         for (int j = 0; j < N; ++j)
             a[j] = S[row * LD + j];
+        if (S[0] < 0.0) // warp uniform: negative definite -> factorise -M, solve with -b
+        {
+#pragma unroll
+            for (int j = 0; j < N; ++j)
+                a[j] = -a[j];
+            y = -y;
+        }
         __syncwarp();
         double rinv = 0.0; // 1 / L[lane][lane]
 #pragma unroll
@@ -646,7 +682,10 @@ __global__ void __launch_bounds__(128) spd_solve_reg_kernel(size_t E, const doub
                 y = fma(-S[lane * LD + k], uk, y);
         }
         if (lane < N)
+        {
             b[lane] = y;
+            spd_flag_if_bad(y, status);
+        }
     }
 }
 
@@ -661,7 +700,7 @@ static void launch_spd_solve_reg(const LaunchCfg &cfg, size_t E, const double *m
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_reg_kernel<N>, 128, smem) != cudaSuccess || per_sm < 1)
         per_sm = 1;
     const size_t blocks = std::min<size_t>((E + 3) / 4, (size_t)cfg.sm_count * per_sm);
-    spd_solve_reg_kernel<N><<<(int)blocks, 128, smem, cfg.stream>>>(E, mass, rhs);
+    spd_solve_reg_kernel<N><<<(int)blocks, 128, smem, cfg.stream>>>(E, mass, rhs, cfg.status);
 }
 
 // Two-block register variant for 33 <= n <= 64 (the C2 space is 49 x 49, a C3 block pair 72 is beyond it): still ONE WARP
@@ -720,7 +759,8 @@ __device__ __forceinline__ void chol_back32(double &y, double rinv, const double
     }
 }
 
-__global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, const double *__restrict__ mass, double *__restrict__ rhs)
+__global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, const double *__restrict__ mass, double *__restrict__ rhs,
+                                                             int *__restrict__ status)
 {
     extern __shared__ __align__(16) double chol_reg2_smem[];
     constexpr int PER_WARP = 2 * 32 * kReg2LD + 32 * kReg2XLD + 32; // S1 | S2 | X | y1
@@ -740,13 +780,15 @@ __global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, co
         double *b = rhs + e * (size_t)n;
         __syncwarp();
         double a[32], x[32];
+        const bool neg = A[0] < 0.0; // negative definite -> factorise -M, solve with -b (a predicate, not a register pair)
+        auto sgn = [neg](double v) { return neg ? -v : v; };
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            a[j] = A[(size_t)lane * n + j];
+            a[j] = sgn(A[(size_t)lane * n + j]);
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            x[j] = A[(size_t)rr * n + j];
-        double y1 = b[lane], y2 = valid ? b[32 + lane] : 0.0;
+            x[j] = sgn(A[(size_t)rr * n + j]);
+        double y1 = sgn(b[lane]), y2 = valid ? sgn(b[32 + lane]) : 0.0;
         const double rinv1 = chol_factor32(a, y1, S1, lane, 32);
         Y1[lane] = y1;
         __syncwarp();
@@ -772,7 +814,7 @@ __global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, co
             double sacc = (j == lane) ? 1.0 : 0.0;
             if (j < n2) // warp uniform
             {
-                sacc = valid ? A[(size_t)rr * n + 32 + j] : sacc;
+                sacc = valid ? sgn(A[(size_t)rr * n + 32 + j]) : sacc;
                 const double *xj = X + j * kReg2XLD;
                 double s0 = 0.0, s1 = 0.0;
 #pragma unroll
@@ -800,6 +842,7 @@ __global__ void __launch_bounds__(128) spd_solve_reg2_kernel(int n, size_t E, co
         b[lane] = y1;
         if (valid)
             b[32 + lane] = y2;
+        spd_flag_if_bad(y1 + (valid ? y2 : 0.0), status);
     }
 }
 
@@ -848,7 +891,8 @@ __device__ __forceinline__ void chol_diag32(double *D, double *rinv_out, int lan
 }
 
 __global__ void __launch_bounds__(256, 2)
-    spd_solve_blocked_kernel(int n, int lda, bool staged, size_t E, double *__restrict__ mass, double *__restrict__ rhs)
+    spd_solve_blocked_kernel(int n, int lda, bool staged, size_t E, double *__restrict__ mass, double *__restrict__ rhs,
+                             int *__restrict__ status)
 {
     extern __shared__ __align__(16) double chol_blk_smem[];
     const int tid = threadIdx.x, lane = tid & 31, nthr = blockDim.x;
@@ -865,16 +909,25 @@ __global__ void __launch_bounds__(256, 2)
         double *A = staged ? As : Ag;
         double *brow = staged ? As + (size_t)n * lda : bg; // row n of the extended matrix
         __syncthreads();
+        const double sg = Ag[0] < 0.0 ? -1.0 : 1.0; // negative definite -> factorise -M, solve with -b
         if (staged)
         {
             for (int idx = tid, i = 0, j = tid; idx < n * n; idx += nthr, j += nthr)
             {
                 while (j >= n)
                     j -= n, ++i;
-                As[i * lda + j] = __ldcs(Ag + idx);
+                As[i * lda + j] = sg * __ldcs(Ag + idx);
             }
             for (int j = tid; j < n; j += nthr)
-                brow[j] = bg[j];
+                brow[j] = sg * bg[j];
+        }
+        else if (sg < 0.0) // in place (the matrix is overwritten by its factor anyway)
+        {
+            __syncthreads(); // every thread has read Ag[0]
+            for (int idx = tid; idx < n * n; idx += nthr)
+                Ag[idx] = -Ag[idx];
+            for (int j = tid; j < n; j += nthr)
+                bg[j] = -bg[j];
         }
         __syncthreads();
         for (int kb = 0; kb < n; kb += kCholNB)
@@ -1025,7 +1078,10 @@ __global__ void __launch_bounds__(256, 2)
             __syncthreads();
         }
         for (int j = tid; j < n; j += nthr)
+        {
             bg[j] = y[j];
+            spd_flag_if_bad(y[j], status);
+        }
     }
 }
 
@@ -1172,7 +1228,7 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
         int per_sm = 0;
         IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_reg2_kernel, 128, smem));
         const size_t blocks = std::min<size_t>((E + 3) / 4, (size_t)cfg.sm_count * std::max(per_sm, 1));
-        spd_solve_reg2_kernel<<<(int)blocks, 128, smem, cfg.stream>>>((int)n, E, mass, rhs);
+        spd_solve_reg2_kernel<<<(int)blocks, 128, smem, cfg.stream>>>((int)n, E, mass, rhs, cfg.status);
         ++*cfg.launch_counter;
         return check_launch("spd_solve_reg2_kernel");
     }
@@ -1191,7 +1247,7 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
         int per_sm = 0;
         IB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, spd_solve_blocked_kernel, threads, smem));
         const size_t grid = std::min<size_t>(E, (size_t)cfg.sm_count * std::max(per_sm, 1));
-        spd_solve_blocked_kernel<<<(int)grid, threads, smem, cfg.stream>>>((int)n, lda, staged, E, mass, rhs);
+        spd_solve_blocked_kernel<<<(int)grid, threads, smem, cfg.stream>>>((int)n, lda, staged, E, mass, rhs, cfg.status);
         ++*cfg.launch_counter;
         return check_launch("spd_solve_blocked_kernel");
     }
@@ -1213,14 +1269,14 @@ int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, d
         const size_t cap = (size_t)cfg.sm_count * std::max(per_sm, 1);
         if (blocks > cap)
             blocks = cap;
-        spd_solve_smem_kernel<<<(int)blocks, 32 * wpc, smem, cfg.stream>>>((int)n, ld, E, mass, rhs);
+        spd_solve_smem_kernel<<<(int)blocks, 32 * wpc, smem, cfg.stream>>>((int)n, ld, E, mass, rhs, cfg.status);
         ++*cfg.launch_counter;
         return check_launch("spd_solve_smem_kernel");
     }
     const size_t cap = (size_t)cfg.sm_count * 16;
     if (blocks > cap)
         blocks = cap;
-    spd_solve_kernel<<<(int)blocks, 128, 0, cfg.stream>>>((int)n, E, mass, rhs);
+    spd_solve_kernel<<<(int)blocks, 128, 0, cfg.stream>>>((int)n, E, mass, rhs, cfg.status);
     ++*cfg.launch_counter;
     return check_launch("spd_solve_kernel");
 }

@@ -12,6 +12,8 @@ things it needs from it are an allocator vtable and a multi-dimensional index it
 
   oracle/_ref/interplib/_interp.<EXT_SUFFIX>   the reference CPython extension
   oracle/_ref/interplib/*.py                    install-time copy of python/interplib
+  oracle/_ref/tests/*.py                        install-time copy of the reference's tests (run unchanged
+                                                against this repo's `interplib` alias, tests/test_dropin_gpu.py)
   oracle/_ref/libinterp_ref.so                  the reference C core (hidden symbols made
                                                 visible with -DINTERPLIB_INTERNAL=) for ctypes
 
@@ -107,6 +109,12 @@ def build(force: bool = False) -> Path:
     _run(["gcc", "-shared", "-fopenmp", *objs["vis"], "-o", str(OUT / "libinterp_ref.so"), "-lm"])
     for f in (REF / "python" / "interplib").glob("*.py*"):
         shutil.copy2(f, pkg / f.name)
+    # install-time copy of the reference's own test-suite: the drop-in acceptance test (tests/test_dropin_gpu.py) runs
+    # these files UNCHANGED against the `interplib` alias of this repo on the GPU box, where /root/reference is absent
+    tests = OUT / "tests"
+    tests.mkdir(parents=True, exist_ok=True)
+    for f in (REF / "tests").glob("*.py"):
+        shutil.copy2(f, tests / f.name)
     return OUT
 
 

@@ -1,5 +1,7 @@
 """Multi-GPU host logic on CPU: the element partition (bit-exact integer bookkeeping) and the two collectives of
-SURVEY 8e -- all-gather of DoF slabs, all-reduce of norms -- over gloo with world size 2 (and 3, uneven tails)."""
+SURVEY 8e -- all-gather of DoF slabs, all-reduce of norms -- over gloo with world size 2 (and 3, uneven tails).  The
+product path runs the same bookkeeping over NCCL through the C ABI (tests/test_partition_gpu.py); gloo stands in for it
+here through tests/_gloo_comm.py."""
 import os
 import socket
 import sys
@@ -10,6 +12,7 @@ import pytest
 
 ROOT = Path(__file__).resolve().parents[1]
 sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
 
 from interplib_b200.partition import ElementPartition, element_range  # noqa: E402
 
@@ -43,10 +46,12 @@ def _free_port() -> int:
 def _worker(rank: int, world: int, port: int, E: int, N: int, tmp: str):
     import torch.distributed as dist
 
+    from _gloo_comm import GlooComm
+
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        part = ElementPartition.from_environment(E)
+        part = ElementPartition.from_comm(E, GlooComm())
         assert (part.world, part.rank) == (world, rank)
         full = np.random.default_rng(42).random((E, N))  # same on every rank
         mine = part.local(full)
@@ -54,10 +59,12 @@ def _worker(rank: int, world: int, port: int, E: int, N: int, tmp: str):
         # each rank "computes" only its slab; the gather must reproduce the full array bit for bit, in element order
         gathered = part.gather_slabs(np.ascontiguousarray(mine))
         assert gathered.shape == (E, N) and np.array_equal(gathered, full)
-        import torch
-
-        g2 = part.gather_slabs(torch.from_numpy(np.ascontiguousarray(mine)))
-        assert torch.equal(g2, torch.from_numpy(full))
+        # pipelined form: sub-slabs of 3 elements of every rank's slab land at their final places
+        piece = np.zeros((E, N))
+        for lo in range(0, part.max_count, 3):
+            counts, offsets = part.slab_layout(N, lo, 3)
+            part.comm.allgatherv(np.ascontiguousarray(mine[lo : lo + 3]), piece, counts, offsets)
+        assert np.array_equal(piece, full)
         # norms: per-rank partial sums -> all-reduce
         sums = part.reduce_sums([float(np.sum(mine * mine)), float(part.count)])
         assert sums[1] == E and abs(sums[0] - np.sum(full * full)) <= 1e-12 * np.sum(full * full)
@@ -77,7 +84,7 @@ def test_gather_and_reduce_over_gloo(tmp_path, world, E):
 
 
 def test_single_process_partition_is_the_identity():
-    part = ElementPartition.from_environment(5)
+    part = ElementPartition.from_comm(5)
     a = np.arange(10.0).reshape(5, 2)
     assert part.world == 1 and part.local(a) is not None and np.array_equal(part.gather_slabs(a), a)
     assert part.reduce_sums([1.5, 2.5]).tolist() == [1.5, 2.5]
