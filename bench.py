@@ -561,13 +561,12 @@ class Runner:
         ms_compute = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, False), steps)
         ms_coll = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, True, compute=False), steps)
         comm.check()
-        norms = d_norm.download((n_sub,))
-        proj_sq = float(np.sum(norms))
 
         # ---- parity of the collective: a 4096-element slab owned by the LAST rank, recomputed by this rank alone, must equal
         # the rows the all-gather delivered, bit for bit (GPUTEST boxes have one GPU: this is the driver-visible NCCL check)
         run_all()
         ctx.synchronize()
+        proj_sq = float(np.sum(d_norm.download((n_sub,))))  # of a whole step (the collective-only pass re-reduces in place)
         chk_n = min(4096, part.counts[-1])
         chk_first = part.offsets[-1]
         c_g, c_f = upload_inputs(chk_first, chk_n)

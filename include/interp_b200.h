@@ -143,6 +143,18 @@ IB200_API int ib200_basis_at_points(basis_spec_t basis, size_t cnt, const double
  * src/python/function_space_objects.c:142-276): out[cnt][N]; x[k] points to cnt coordinates. */
 IB200_API int ib200_function_space_evaluate(unsigned ndim, const basis_spec_t *basis, size_t cnt,
                                             const double *const *x, double *out);
+/* src/polynomials on caller-supplied nodes -- the module-level functions of the extension (src/python/module.c:102-560):
+ * lagrange1d / dlagrange1d / d2lagrange1d = out[cnt][n_roots], derivative = 0 / 1 / 2
+ * (lagrange_polynomial_values, _first_derivative, _second_derivative: src/polynomials/lagrange.c:59-106, 317-381, 739-808) */
+IB200_API int ib200_lagrange_samples(unsigned n_roots, const double *roots, size_t cnt, const double *x, unsigned derivative,
+                                     double *out);
+/* compute_gll(order, max_iter, tol) (src/python/module.c:559-621; src/integration/gauss_lobatto.c:14-61) */
+IB200_API int ib200_gauss_lobatto(unsigned order, unsigned max_iter, double tol, double *nodes, double *weights,
+                                  int *non_converged);
+/* bernstein1d(order, t) = out[cnt][order+1] on the unit interval (src/python/module.c:646-686; bernstein.c:31-51) and
+ * bernstein_coefficients (in place power series -> Bernstein, src/python/module.c:706-718; bernstein.c:8-29) */
+IB200_API int ib200_bernstein_samples(unsigned order, size_t cnt, const double *t, double *out);
+IB200_API int ib200_bernstein_from_power_series(unsigned n, double *coefficients);
 
 /* ---- context ---------------------------------------------------------------------------- */
 

@@ -456,3 +456,35 @@ def function_space_evaluate(basis, xs):
     ptrs = (_lib._dp * len(xs))(*[x.ctypes.data_as(_lib._dp) for x in xs])
     check(lib.ib200_function_space_evaluate(len(basis), basis_specs(basis), xs[0].size, ptrs, out.ctypes.data_as(_lib._dp)))
     return out
+
+
+# ---- src/polynomials on caller-supplied nodes (host table layer) ----------------------------------------------------
+def lagrange_samples(roots, x, deriv: int) -> np.ndarray:
+    """out[len(x)][len(roots)] = d^deriv l_j / dx^deriv at x (ib200_lagrange_samples)."""
+    roots = np.ascontiguousarray(roots, dtype=np.float64)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    out = np.empty((x.size, roots.size))
+    check(lib.ib200_lagrange_samples(roots.size, roots.ctypes.data_as(C.c_void_p), x.size, x.ctypes.data_as(C.c_void_p),
+                                     int(deriv), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def gauss_lobatto(order: int, max_iter: int, tol: float):
+    """(nodes, weights, non-converged node count) of the (order+1)-point Gauss-Lobatto rule (ib200_gauss_lobatto)."""
+    nodes, weights, bad = np.empty(order + 1), np.empty(order + 1), C.c_int(0)
+    check(lib.ib200_gauss_lobatto(int(order), int(max_iter), float(tol), nodes.ctypes.data_as(C.c_void_p),
+                                  weights.ctypes.data_as(C.c_void_p), C.byref(bad)))
+    return nodes, weights, int(bad.value)
+
+
+def bernstein_samples(order: int, t) -> np.ndarray:
+    t = np.ascontiguousarray(t, dtype=np.float64)
+    out = np.empty((t.size, order + 1))
+    check(lib.ib200_bernstein_samples(int(order), t.size, t.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
+def bernstein_from_power_series(coeffs: np.ndarray) -> np.ndarray:
+    """In place on a contiguous float64 array (ib200_bernstein_from_power_series); returns it."""
+    check(lib.ib200_bernstein_from_power_series(coeffs.size, coeffs.ctypes.data_as(C.c_void_p)))
+    return coeffs

@@ -182,6 +182,40 @@ extern "C" int ib200_basis_at_points(basis_spec_t basis, size_t cnt, const doubl
     return ib200_tables_basis_at_points(basis, cnt, x, values, derivatives);
 }
 
+extern "C" int ib200_lagrange_samples(unsigned n_roots, const double *roots, size_t cnt, const double *x, unsigned derivative,
+                                      double *out)
+{
+    if (derivative > 2)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "derivative order must be 0, 1 or 2, got %u", derivative);
+    if ((n_roots && !roots) || (cnt && !x) || (cnt && n_roots && !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "roots/x/out must not be NULL");
+    return ib200_tables_lagrange_samples(n_roots, roots, cnt, x, derivative, out);
+}
+
+extern "C" int ib200_gauss_lobatto(unsigned order, unsigned max_iter, double tol, double *nodes, double *weights,
+                                   int *non_converged)
+{
+    if (!nodes || !weights)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "nodes/weights must not be NULL");
+    if (!(tol >= 0.0))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "tolerance must not be negative");
+    return ib200_tables_gauss_lobatto(order, max_iter, tol, nodes, weights, non_converged);
+}
+
+extern "C" int ib200_bernstein_samples(unsigned order, size_t cnt, const double *t, double *out)
+{
+    if (cnt && (!t || !out))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "t/out must not be NULL");
+    return ib200_tables_bernstein_samples(order, cnt, t, out);
+}
+
+extern "C" int ib200_bernstein_from_power_series(unsigned n, double *coefficients)
+{
+    if (n && !coefficients)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "coefficients must not be NULL");
+    return ib200_tables_bernstein_from_power(n, coefficients);
+}
+
 extern "C" int ib200_function_space_evaluate(unsigned ndim, const basis_spec_t *basis, size_t cnt,
                                              const double *const *x, double *out)
 {

@@ -107,10 +107,11 @@ static void gauss_legendre(unsigned n, double tol, unsigned max_iter, double *x,
     }
 }
 
-static void gauss_lobatto(unsigned n, double tol, unsigned max_iter, double *x, double *w)
+static int gauss_lobatto(unsigned n, double tol, unsigned max_iter, double *x, double *w)
 {
+    int non_converged = 0; /* nodes whose last Newton step was still above tol (the reference's return value) */
     if (trivial_rule(n, x, w))
-        return;
+        return 0;
     x[0] = -1.0;
     x[n - 1] = +1.0;
     if (w)
@@ -133,6 +134,7 @@ static void gauss_lobatto(unsigned n, double tol, unsigned max_iter, double *x, 
             xi -= step;
             err = fabs(step);
         }
+        non_converged += (err > tol);
         x[n - i] = xi;
         if (w)
         {
@@ -141,6 +143,7 @@ static void gauss_lobatto(unsigned n, double tol, unsigned max_iter, double *x, 
             w[n - i] = 2.0 / ((double)(n * (n - 1)) * pn * pn);
         }
     }
+    return non_converged;
 }
 
 int ib200_tables_rule(integration_spec_t spec, double *nodes, double *weights, unsigned *accuracy)
@@ -747,3 +750,104 @@ int ib200_tables_incidence_matrix(basis_spec_t basis, double *out)
     }
 }
 
+
+/* ---- src/polynomials on arbitrary roots (what lagrange1d / dlagrange1d / d2lagrange1d of the extension expose,
+ *      src/python/module.c:102-560) ------------------------------------------------------------------------------
+ * out[p][j] = d^k/dx^k l_j(x_p) for k = deriv in {0, 1, 2}.  The reference multiplies the numerator sums by the
+ * RECIPROCAL of the product denominator here (lagrange_polynomial_values / _first_derivative / _second_derivative,
+ * src/polynomials/lagrange.c:59-106, 317-381, 739-808), unlike the table routines above, which divide. */
+int ib200_tables_lagrange_samples(unsigned n, const double *roots, size_t cnt, const double *x, unsigned deriv, double *out)
+{
+    if (deriv > 2)
+        return INTERP_ERROR_BAD_SYSTEM;
+    if (n == 0 || cnt == 0)
+        return INTERP_SUCCESS;
+    double *buf = malloc(sizeof(double) * 2 * n);
+    if (!buf)
+        return INTERP_ERROR_FAILED_ALLOCATION;
+    double *rden = buf, *dif = buf + n;
+    for (unsigned j = 0; j < n; ++j)
+        rden[j] = 1.0 / lagrange_denominator(n, roots, j);
+    for (size_t p = 0; p < cnt; ++p)
+    {
+        double *row = out + p * n;
+        if (deriv == 0)
+        {
+            for (unsigned j = 0; j < n; ++j)
+                row[j] = lagrange_value(n, roots, j, x[p], 1.0, 0) * rden[j];
+            continue;
+        }
+        if (deriv == 1)
+            lagrange_derivative_numerators(n, roots, x[p], dif, row);
+        else
+        {
+            /* every unordered triple {i > j > k} contributes twice the product of the other differences to each of
+             * its three members, in the order k, j, i */
+            for (unsigned j = 0; j < n; ++j)
+            {
+                dif[j] = x[p] - roots[j];
+                row[j] = 0.0;
+            }
+            for (unsigned i = 0; i < n; ++i)
+                for (unsigned j = 0; j < i; ++j)
+                    for (unsigned k = 0; k < j; ++k)
+                    {
+                        double prod = 1.0;
+                        for (unsigned l = 0; l < n; ++l)
+                            if (l != i && l != j && l != k)
+                                prod *= dif[l];
+                        row[k] += 2 * prod;
+                        row[j] += 2 * prod;
+                        row[i] += 2 * prod;
+                    }
+        }
+        for (unsigned j = 0; j < n; ++j)
+            row[j] *= rden[j];
+    }
+    free(buf);
+    return INTERP_SUCCESS;
+}
+
+/* compute_gll (src/python/module.c:559-621 -> gauss_lobatto_nodes_weights, src/integration/gauss_lobatto.c:14-61) with
+ * the caller's iteration limit and tolerance; *non_converged = nodes whose last Newton step was still above tol. */
+int ib200_tables_gauss_lobatto(unsigned order, unsigned max_iter, double tol, double *nodes, double *weights,
+                               int *non_converged)
+{
+    const int bad = gauss_lobatto(order + 1, tol, max_iter, nodes, weights);
+    if (non_converged)
+        *non_converged = bad;
+    return INTERP_SUCCESS;
+}
+
+/* bernstein1d (src/python/module.c:646-686): out[p][0..order] = Bernstein polynomials of degree `order` at t = x[p]
+ * in [0, 1] (NOT mapped from [-1, 1]: the extension function takes the unit-interval coordinate) */
+int ib200_tables_bernstein_samples(unsigned order, size_t cnt, const double *t, double *out)
+{
+    for (size_t p = 0; p < cnt; ++p)
+        bernstein_vector(t[p], order, out + p * (order + 1));
+    return INTERP_SUCCESS;
+}
+
+/* bernstein_coefficients (src/python/module.c:706-718 -> bernstein_from_power_series, src/polynomials/bernstein.c:8-29):
+ * power-series coefficients a_k of a degree m = n-1 polynomial -> Bernstein coefficients, in place, by forward
+ * elimination: B^m_k(t) = C(m,k) sum_i (-1)^i C(m-k,i) t^(k+i), so once c_k = r_k / C(m,k) is known (r = running
+ * residual) its higher powers are removed from the residual: r_(k+i) += r_k * (-1)^(i+1) C(m-k,i). */
+int ib200_tables_bernstein_from_power(unsigned n, double *c)
+{
+    const int m = (int)n - 1;
+    unsigned binom = 1; /* C(m, k) */
+    for (int k = 0; k <= m; ++k)
+    {
+        const double resid = c[k];
+        const int rest = m - k;
+        int alt = rest; /* (-1)^(i+1) C(rest, i), i = 1 */
+        for (int i = 1; i <= rest; ++i)
+        {
+            c[k + i] += resid * (double)alt;
+            alt = (alt * (i - rest)) / (i + 1);
+        }
+        c[k] = resid / (double)binom;
+        binom = (binom * (unsigned)rest) / (unsigned)(k + 1);
+    }
+    return INTERP_SUCCESS;
+}

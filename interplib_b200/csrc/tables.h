@@ -22,6 +22,11 @@ int ib200_tables_function_space_evaluate(unsigned ndim, const basis_spec_t *basi
                                          const double *const *x, double *out);
 
 int ib200_tables_incidence_matrix(basis_spec_t basis, double *out);
+int ib200_tables_lagrange_samples(unsigned n, const double *roots, size_t cnt, const double *x, unsigned deriv, double *out);
+int ib200_tables_gauss_lobatto(unsigned order, unsigned max_iter, double tol, double *nodes, double *weights,
+                               int *non_converged);
+int ib200_tables_bernstein_samples(unsigned order, size_t cnt, const double *t, double *out);
+int ib200_tables_bernstein_from_power(unsigned n, double *c);
 
 #ifdef __cplusplus
 }

@@ -670,11 +670,136 @@ def compute_dual_degrees_of_freedom(fn: Callable, integration_space: Integration
     return projection_l2_dual(fn, function_space, integration_space)
 
 
+# ------------------------------------------------------------------------------------------------ src/polynomials
+def _lagrange_samples(roots, x, out, deriv: int) -> np.ndarray:
+    """Shared body of lagrange1d / dlagrange1d (src/python/module.c:102-199, 307-404): ``roots`` 1-D, ``x`` any shape,
+    result ``x.shape + (len(roots),)``; an ``out`` array is checked like the extension does and returned itself."""
+    roots = np.ascontiguousarray(roots, dtype=np.float64)
+    if roots.ndim != 1:
+        raise ValueError("Roots must be a one-dimensional array.")
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    shape = x.shape + (roots.size,)
+    if out is not None:
+        if not isinstance(out, np.ndarray):
+            raise TypeError(f"out must be a numpy array, not {type(out).__name__}")
+        if out.dtype != np.float64:
+            raise ValueError("Output array must have the correct type (numpy.double/numpy.float64).")
+        if out.shape != shape:
+            raise ValueError("Output must have same shape as input array, except for one more dimension, which must be "
+                             "the same length as the array of Lagrange nodes.")
+    res = batch.lagrange_samples(roots, x.reshape(-1), deriv).reshape(shape)
+    if out is None:
+        return res
+    out[...] = res
+    return out
+
+
+def lagrange1d(roots, x, out=None, /) -> np.ndarray:
+    """Lagrange polynomials with nodes ``roots`` at ``x`` (src/python/module.c:102-199)."""
+    return _lagrange_samples(roots, x, out, 0)
+
+
+def dlagrange1d(roots, x, out=None, /) -> np.ndarray:
+    """First derivatives of the Lagrange polynomials (src/python/module.c:307-404)."""
+    return _lagrange_samples(roots, x, out, 1)
+
+
+def d2lagrange1d(x, xp, /) -> np.ndarray:
+    """Second derivatives, ``[len(x), len(xp)]``; note the argument order: points first, nodes second, both 1-D float64
+    arrays (src/python/module.c:514-557)."""
+    if not isinstance(x, np.ndarray) or not isinstance(xp, np.ndarray):
+        raise TypeError("d2lagrange1d() arguments must be numpy arrays")
+    if x.dtype != np.float64 or xp.dtype != np.float64 or x.ndim != 1 or xp.ndim != 1:
+        raise ValueError("x and xp must be one-dimensional float64 arrays")
+    return batch.lagrange_samples(np.ascontiguousarray(xp), np.ascontiguousarray(x), 2)
+
+
+def bernstein1d(n: int, x, /) -> np.ndarray:
+    """Bernstein polynomials of degree ``n`` on the unit interval, ``[len(x), n+1]`` (src/python/module.c:646-686)."""
+    if int(n) < 0:
+        raise OverflowError("can't convert negative value to unsigned int")
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    if x.ndim != 1:
+        raise ValueError("x must be a one-dimensional array")
+    return batch.bernstein_samples(int(n), x)
+
+
+def bernstein_coefficients(x, /) -> np.ndarray:
+    """Power-series coefficients -> Bernstein coefficients of the same polynomial (src/python/module.c:706-718)."""
+    c = np.array(x, dtype=np.float64, order="C")  # always a copy, like NPY_ARRAY_ENSURECOPY
+    if c.ndim != 1:
+        raise ValueError("x must be a one-dimensional array")
+    return batch.bernstein_from_power_series(c)
+
+
+def compute_gll(order: int, max_iter: int = 10, tol: float = 1e-15) -> tuple[np.ndarray, np.ndarray]:
+    """Gauss-Legendre-Lobatto nodes and weights (src/python/module.c:559-621).  A node that does not converge raises
+    RuntimeWarning, as the extension does (it sets the exception rather than issuing a warning)."""
+    order, max_iter, tol = int(order), int(max_iter), float(tol)
+    if order < 0:
+        raise ValueError(f"Order must be positive, but was given as {order}.")
+    if max_iter < 0:
+        raise ValueError(f"Number of maximum iterations must be positive, but was given as {max_iter}.")
+    if tol < 0:
+        raise ValueError(f"Tolerance must be positive {tol:g}")
+    nodes, weights, bad = batch.gauss_lobatto(order, max_iter, tol)
+    if bad:
+        raise RuntimeWarning(f"A total of {bad} nodes were non-converged. Consider changing the tolerance or increase the "
+                             "number of iterations.")
+    return nodes, weights
+
+
+__all__ += ["lagrange1d", "dlagrange1d", "d2lagrange1d", "bernstein1d", "bernstein_coefficients", "compute_gll"]
+
+
+def _sample_matrix(x, xp, deriv: int) -> np.ndarray:
+    """``[N, M]`` matrix taking samples ``f(xp)`` to the ``deriv``-th derivative of their interpolant at the flattened
+    ``x`` (python/interplib/lagrange.py:18-101)."""
+    flat = np.ravel(np.atleast_1d(np.asarray(x, np.float64)), order="C")
+    nodes = np.asarray(xp, np.float64)
+    return d2lagrange1d(np.ascontiguousarray(flat), np.ascontiguousarray(nodes)) if deriv == 2 else _lagrange_samples(nodes, flat, None, deriv)
+
+
+def lagrange_function_samples(x, xp) -> np.ndarray:
+    return _sample_matrix(x, xp, 0)
+
+
+def lagrange_derivative_samples(x, xp) -> np.ndarray:
+    return _sample_matrix(x, xp, 1)
+
+
+def lagrange_2derivative_samples(x, xp) -> np.ndarray:
+    return _sample_matrix(x, xp, 2)
+
+
+def _interp1d(x, xp, yp, deriv: int) -> np.ndarray:
+    """python/interplib/lagrange.py:104-205: interpolant (or its derivative) through ``(xp, yp)`` evaluated at ``x``."""
+    x, xp, yp = np.asarray(x, np.float64), np.asarray(xp, np.float64), np.asarray(yp, np.float64)
+    if xp.ndim != 1 or yp.ndim != 1 or xp.shape != yp.shape:
+        raise ValueError("Both xp and yp must be flat arrays of equal length")
+    return np.reshape(_sample_matrix(x, xp, deriv) @ yp, x.shape).astype(np.float64, copy=False)
+
+
+def interp1d_function_samples(x, xp, yp) -> np.ndarray:
+    return _interp1d(x, xp, yp, 0)
+
+
+def interp1d_derivative_samples(x, xp, yp) -> np.ndarray:
+    return _interp1d(x, xp, yp, 1)
+
+
+def interp1d_2derivative_samples(x, xp, yp) -> np.ndarray:
+    return _interp1d(x, xp, yp, 2)
+
+
+__all__ += ["lagrange_function_samples", "lagrange_derivative_samples", "lagrange_2derivative_samples",
+            "interp1d_function_samples", "interp1d_derivative_samples", "interp1d_2derivative_samples"]
+
+
 # ------------------------------------------------------------------------------------------------ geometry authoring
 class HypercubeDomain:
     """An element described by one DoF set per physical coordinate; calling it with an IntegrationSpace builds
-    the SpaceMap (python/interplib/domains.py:28-78).  Only the part of the reference's ``domains`` module that
-    produces the hot path's geometry input is mirrored (straight lines and bilinear quads)."""
+    the SpaceMap (python/interplib/domains.py:28-199)."""
 
     def __init__(self, *dofs: DegreesOfFreedom):
         if not dofs:
@@ -694,13 +819,54 @@ class HypercubeDomain:
                  basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> SpaceMap:
         return SpaceMap(*(CoordinateMap(d, space, integration_registry, basis_registry) for d in self.dofs))
 
+    def __eq__(self, other):
+        return isinstance(other, HypercubeDomain) and len(self.dofs) == len(other.dofs) and all(
+            a.function_space == b.function_space and np.array_equal(a.values, b.values) for a, b in zip(self.dofs, other.dofs))
+
+    __hash__ = None
+
     @property
     def geometry_dofs(self) -> np.ndarray:
         """[n_phys][N_g]: one row of the batched API's ``geom_dofs[E][n_phys][N_g]``."""
         return np.stack([d.values.reshape(-1) for d in self.dofs])
 
+    @property
+    def endpoints(self) -> tuple[np.ndarray, ...]:
+        """Coordinates of the 2^d corners: every coordinate reconstructed on the 2-point Lobatto rule per dimension."""
+        corners = IntegrationSpace(*(IntegrationSpecs(1, "gauss-lobatto") for _ in range(self.ndim_reference)))
+        return tuple(d.reconstruct_at_integration_points(corners) for d in self.dofs)
+
+    def compute_size(self, int_space: IntegrationSpace | None = None, *,
+                     integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                     basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> float:
+        """Length / area / volume: sum of weight * det J over a rule that integrates the Jacobian exactly."""
+        if int_space is None:
+            int_space = IntegrationSpace(*(IntegrationSpecs((order + 1) // 2) for order in self.function_space.orders))
+        smap = self(int_space, integration_registry=integration_registry, basis_registry=basis_registry)
+        return float(np.sum(int_space.weights(integration_registry) * smap.determinant))
+
     def sample(self, *x) -> tuple[np.ndarray, ...]:
         return tuple(reconstruct(d, *x) for d in self.dofs)
+
+    def integrate(self, fn: Callable, int_space: IntegrationSpace, *,
+                  integration_registry: IntegrationRegistry = DEFAULT_INTEGRATION_REGISTRY,
+                  basis_registry: BasisRegistry = DEFAULT_BASIS_REGISTRY) -> float:
+        return integrate_callable(fn, self(int_space, integration_registry=integration_registry, basis_registry=basis_registry),
+                                  registry=integration_registry)
+
+    def subregion(self, *ranges: tuple[float, float]) -> "HypercubeDomain":
+        """The part of the domain whose reference coordinates lie in the given (low, high) pairs (missing trailing
+        pairs = the whole [-1, 1]), re-interpolated on uniform Lagrange nodes of the same DoF shape."""
+        d = self.ndim_reference
+        if len(ranges) < d:  # reference quirk kept: fewer pairs than dimensions is the error, despite the wording
+            raise ValueError(f"At most {d} pairs of divisions can be specified.")
+        limits = [(float(lo), float(hi)) for lo, hi in ranges] + [(-1.0, +1.0)] * max(0, d - len(ranges))
+        shape = self.dofs[0].shape
+        if len(limits) != len(shape):
+            raise ValueError("zip() argument lengths differ")
+        grid = np.meshgrid(*(np.linspace(lo, hi, n) for n, (lo, hi) in zip(shape, limits)), indexing="ij")
+        fs = FunctionSpace(*(BasisSpecs(BasisType.LAGRANGE_UNIFORM, n - 1) for n in shape))
+        return HypercubeDomain(*(DegreesOfFreedom(fs, vals) for vals in self.sample(*grid)))
 
 
 class Line(HypercubeDomain):
@@ -708,32 +874,61 @@ class Line(HypercubeDomain):
     (python/interplib/domains.py:200-233)."""
 
     def __init__(self, *knots):
-        pts = np.array(knots, dtype=np.float64)
+        pts = np.array(knots)
         if pts.ndim != 2:
             raise ValueError("Line must be specified by an array of points.")
         if pts.shape[0] < 2:
             raise ValueError("At least two points must be given for a line.")
-        fs = FunctionSpace(BasisSpecs("bernstein", pts.shape[0] - 1))
+        fs = FunctionSpace(BasisSpecs(BasisType.BERNSTEIN, pts.shape[0] - 1))
         self.knots = pts
         super().__init__(*(DegreesOfFreedom(fs, pts[:, k]) for k in range(pts.shape[1])))
 
-    start = property(lambda self: self.knots[0])
-    end = property(lambda self: self.knots[-1])
+    start = property(lambda self: self.knots[0, :])
+    end = property(lambda self: self.knots[-1, :])
+
+    def reverse(self) -> "Line":
+        return Line(*self.knots[::-1])
 
 
 class Quad(HypercubeDomain):
-    """Straight-sided quadrilateral: ``lagrange-uniform`` order-1 DoFs ``[i0][i1]`` per coordinate with the corner at
-    reference position (2*i0-1, 2*i1-1) -- what ``Quad.from_corners`` of the reference produces for linear edges
-    (python/interplib/domains.py:236-331); curved-edge blending is geometry authoring outside the hot path."""
+    """Quadrilateral bounded by four :class:`Line` s given counter-clockwise (bottom, right, top, left), each starting
+    where the previous one ends (python/interplib/domains.py:236-331).  Its coordinates are the transfinite (Coons)
+    interpolant of the edges on uniform Lagrange nodes: edge contributions blended linearly across the opposite
+    direction, minus the bilinear interpolant of the corners, which the two blends count twice."""
 
-    def __init__(self, *dofs: DegreesOfFreedom):
+    def __init__(self, bottom: Line, right: Line, top: Line, left: Line):
+        edges = (bottom, right, top, left)
+        for ln in edges:
+            if type(ln) is not Line:
+                raise TypeError(f"Only {Line} objects can be used as inputs for a Quad")
+        for prev, nxt, msg in ((bottom, right, "The right side does not start where the bottom ends."),
+                               (right, top, "The top side does not start where the right ends."),
+                               (top, left, "The left side does not start where the top ends."),
+                               (left, bottom, "The bottom side does not start where the left ends.")):
+            if np.any(prev.end != nxt.start):
+                raise ValueError(msg)
+        n_h = max(1, bottom.function_space.orders[0], top.function_space.orders[0])
+        n_v = max(1, right.function_space.orders[0], left.function_space.orders[0])
+        fs = FunctionSpace(BasisSpecs(BasisType.LAGRANGE_UNIFORM, n_h), BasisSpecs(BasisType.LAGRANGE_UNIFORM, n_v))
+        xi, eta = np.linspace(-1, +1, n_h + 1), np.linspace(-1, +1, n_v + 1)
+        # the top and left edges run against their reference direction
+        on_b, on_r, on_t, on_l = bottom.sample(xi), right.sample(eta), top.sample(xi[::-1]), left.sample(eta[::-1])
+        # blending weights on the [eta][xi] grid, written like the reference does ((1 -/+ s) / 2) so that the DoFs
+        # round the same way
+        lo_x, hi_x = ((1 - xi) / 2)[None, :], ((1 + xi) / 2)[None, :]
+        lo_y, hi_y = ((1 - eta) / 2)[:, None], ((1 + eta) / 2)[:, None]
+        dofs = []
+        for b, r, t, l, c_bl, c_br, c_tr, c_tl in zip(on_b, on_r, on_t, on_l, bottom.start, right.start, top.start, left.start):
+            edges_part = b[None, :] * lo_y + r[:, None] * hi_x + t[None, :] * hi_y + l[:, None] * lo_x
+            corner_part = c_bl * lo_y * lo_x + c_br * lo_y * hi_x + c_tr * hi_y * hi_x + c_tl * hi_y * lo_x
+            dofs.append(DegreesOfFreedom(fs, (edges_part - corner_part).T))
         super().__init__(*dofs)
 
     @classmethod
     def from_corners(cls, bottom_left, bottom_right, top_right, top_left) -> "Quad":
-        bl, br, tr, tl = (np.asarray(p, dtype=np.float64) for p in (bottom_left, bottom_right, top_right, top_left))
-        fs = FunctionSpace(BasisSpecs("lagrange-uniform", 1), BasisSpecs("lagrange-uniform", 1))
-        return cls(*(DegreesOfFreedom(fs, np.array([[bl[k], tl[k]], [br[k], tr[k]]])) for k in range(bl.shape[0])))
+        """Straight-sided quad through four corners."""
+        return cls(bottom=Line(bottom_left, bottom_right), right=Line(bottom_right, top_right),
+                   top=Line(top_right, top_left), left=Line(top_left, bottom_left))
 
 
 __all__ += ["HypercubeDomain", "Line", "Quad"]

@@ -138,8 +138,9 @@ class CpuArm:
     def calibrate(self, target_s: float, cap: int = 1 << 22) -> int:
         """Elements per step so that one step takes about target_s (at most `cap`)."""
         n = self.effective_count(max(self.cores * 4, 8))
+        self.run(n)  # first call: imports, table caches, page faults -- not representative
         t = self.run(n)
-        while t < 0.2 and n < cap:
+        while t < 0.5 and n < cap:
             n *= 4
             t = self.run(n)
         return self.effective_count(max(self.cores, min(cap, int(n * target_s / max(t, 1e-9)))))
