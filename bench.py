@@ -48,8 +48,8 @@ from interplib_b200 import synthetic as syn  # noqa: E402  (pure NumPy: does not
 NCU_TRAFFIC_BYTES = {
     "c2": (1970064432, 1 << 20),   # profiles/r01e_c2_eval2d_full.txt
     "c5": (5249943208, 1 << 20),   # profiles/r01c_c5_mass2d_lo_full.txt
-    "c4": (43748198408, 1 << 16),  # profiles/r01e_c4_mass2d_mma_full.txt
-    "c3": (11733279000, 1 << 18),  # profiles/r01e_c3_mass2d_full.txt
+    "c4": None,
+    "c3": None,
     "c1": None,
 }
 METRIC = {"c2": "basis_grad_evals_per_s"}
@@ -78,7 +78,7 @@ def fp64_peak():
 def workload_config(name: str, elements_per_gpu: int) -> dict:
     """The `config` object: names the workload only, so the repo arm and the reference arm print the same one."""
     cfg = syn.CONFIGS[name]
-    per_elem = {"c2": 8 * (cfg.N + 3 * cfg.Q), "c3": 8 * (8 + 4 * 72 * 72)}.get(name, 8 * (8 + cfg.Q + cfg.N * cfg.N + cfg.N))
+    per_elem = {"c2": 8 * (cfg.N + 3 * cfg.Q), "c3": 8 * (8 + 144 * 144)}.get(name, 8 * (8 + cfg.Q + cfg.N * cfg.N + cfg.N))
     return {"workload": f"{cfg.name}: {cfg.description}", "elements_per_gpu": int(elements_per_gpu),
             "basis": [list(b) for b in cfg.basis], "rule": [list(r) for r in cfg.rules],
             "l2": f"inputs+outputs larger than L2 ({(per_elem * elements_per_gpu) >> 20} MiB per step vs 126 MB L2)",
@@ -111,16 +111,16 @@ class Workload:
             self.dominant_bytes_per_elem = self.bytes_per_elem
             self.dominant_is_step = True
         elif name == "c3":
-            # the four determinant-weighted blocks M_ab = compute_mass_matrix(space_b, space_a, smap) of the 2-D 1-form
-            # basis (SURVEY 8c caveat): geometry[E][2][4] -> M[E][144][144] in ONE launch (ib200_kform_mass_mapped_batch)
+            # the determinant-weighted mass matrix of the 2-D 1-form basis (blocks M_ab = compute_mass_matrix(space_b, space_a,
+            # smap), SURVEY 8c caveat): geometry[E][2][4] -> M[E][144][144] in ONE launch (ib200_kform_mass_mapped_batch)
             first = (rank * E) % max(cfg.n_elements - E + 1, 1)
             self.h_in = {"geom": syn.geometry(cfg, first=first, count=E)}
-            self.blocks = [(a, b, list(sa), list(sb)) for a, sa in enumerate(syn.C3_SPACES) for b, sb in enumerate(syn.C3_SPACES)]
-            self.out_shapes = {f"block_{a}{b}": (E, 72, 72) for a, b, _, _ in self.blocks}
-            self.bytes_per_elem = 8 * (8 + 4 * 72 * 72)
-            self.dominant = "mass2d_kernel (K2, one 72x72 block per launch, 4 launches per step)"
-            self.dominant_bytes_per_elem = 8 * (8 + 72 * 72)
-            self.dominant_is_step = False
+            self.kform_basis = [("lagrange-gauss-lobatto", 8)] * 2
+            self.out_shapes = {"mass": (E, 144, 144)}
+            self.bytes_per_elem = 8 * (8 + 144 * 144)
+            self.dominant = "mass2d_kron_kernel<2,9> (K2-kron: the whole 144x144 1-form matrix per element, geometry fused, one launch)"
+            self.dominant_bytes_per_elem = self.bytes_per_elem
+            self.dominant_is_step = True
         else:
             # mass matrix (+ L2 right-hand side): geometry[E][2][4] (+ f[E][Q]) -> M[E][N][N] (+ b[E][N])
             first = (rank * E) % max(cfg.n_elements - E + 1, 1)
@@ -133,7 +133,7 @@ class Workload:
             self.bytes_per_elem = 8 * (geom[0].size + Q + N * N + N)
             fused = name == "c5"  # low order: geometry + mass + right-hand side are ONE kernel, which is then the step
             self.dominant = ({"c5": "mass2d_lo_kernel (K2-lo: geometry + mass matrix + L2 right-hand side fused)",
-                              "c4": "mass2d_mma_kernel (K2-hi DMMA, geometry fused)"}
+                              "c4": "mass2d_kron_kernel<1,17> (K2-kron, geometry fused)"}
                              .get(name, "mass2d_kernel (K2, geometry fused)") if cfg.ndim == 2 else "geometry + mass kernels (1-D generic)")
             self.dominant_bytes_per_elem = self.bytes_per_elem if fused else 8 * (geom[0].size + N * N)
             self.dominant_is_step = fused
@@ -162,9 +162,8 @@ class Workload:
             c.reconstruct(self.basis, self.rules, self.d_in["dofs"].ptr, [0, 1, 2], out=self.d_out["out"].ptr, where=DEVICE,
                           n_elements=self.E)
         elif self.name == "c3":
-            for a, b, sa, sb in (self.blocks[:1] if dominant_only else self.blocks):
-                c.mass_matrix_mapped(sb, sa, self.rules, self.gb, self.d_in["geom"].ptr, 2, out=self.d_out[f"block_{a}{b}"].ptr,
-                                     where=DEVICE, n_elements=self.E)
+            c.kform_mass_mapped(self.kform_basis, 1, self.rules, self.gb, self.d_in["geom"].ptr, 2, 144, out=self.d_out["mass"].ptr,
+                                where=DEVICE, n_elements=self.E)
         else:
             if dominant_only and not self.dominant_is_step:
                 c.mass_matrix_mapped(self.basis, self.basis, self.rules, self.gb, self.d_in["geom"].ptr, self.cfg.n_phys,
@@ -197,9 +196,8 @@ class Workload:
             c.reconstruct(self.basis, self.rules, self.p_in["dofs"].array, [0, 1, 2], out=self.p_out["out"].array)
             return float(self.p_out["out"].array[-1, 0, 0])
         if self.name == "c3":
-            for a, b, sa, sb in self.blocks:
-                c.mass_matrix_mapped(sb, sa, self.rules, self.gb, self.p_in["geom"].array, 2, out=self.p_out[f"block_{a}{b}"].array)
-            return float(self.p_out["block_11"].array[-1, 0, 0])
+            c.kform_mass_mapped(self.kform_basis, 1, self.rules, self.gb, self.p_in["geom"].array, 2, 144, out=self.p_out["mass"].array)
+            return float(self.p_out["mass"].array[-1, 0, 0])
         c.l2_system_mapped(self.basis, self.rules, self.gb, self.p_in["geom"].array, self.cfg.n_phys, self.p_in["fvals"].array,
                            mass=self.p_out["mass"].array, rhs=self.p_out["rhs"].array)
         return float(self.p_out["rhs"].array[-1, 0])

@@ -187,6 +187,13 @@ IB200_API int ib200_ctx_set_mma_min_points(ib200_ctx_t *ctx, int points);
 /* compile-time specialised low-order mass kernel (kernels_mass2d_lo.cu) on/off; default on, $IB200_NO_LO_KERNEL=1
  * turns it off.  Tuning/testing aid: with it off the run-time-shaped kernel serves the same shapes. */
 IB200_API int ib200_ctx_set_lo_kernel(ib200_ctx_t *ctx, int on);
+/* determinant-weighted mass matrices of bilinear quads as a sum of three Kronecker products of 1-D moment tables
+ * (kernels_mass2d_kron.cu: 2 FP64 operations per entry) on/off; default on, $IB200_NO_KRON=1 turns it off: the
+ * sum-factorised kernels (DFMA / DMMA stage 2) then serve the same shapes, as they do for every other weight. */
+IB200_API int ib200_ctx_set_kron(ib200_ctx_t *ctx, int on);
+/* primal L2 projections of bilinear quads by fast diagonalisation (kernels_fastdiag.cu) on/off; default on,
+ * $IB200_NO_FASTDIAG=1 turns it off: ib200_l2_project_mapped_batch then assembles and factorises every mass matrix. */
+IB200_API int ib200_ctx_set_fastdiag(ib200_ctx_t *ctx, int on);
 /* host-pointer calls: elements per staged chunk (0 = automatic) */
 IB200_API int ib200_ctx_set_chunk_elements(ib200_ctx_t *ctx, size_t elements);
 
@@ -306,6 +313,17 @@ IB200_API int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, co
                                              const double *geom_dofs, int idx_in, int idx_out, double *out,
                                              int where);
 
+/* The whole k-form element mass matrix in one call: out[E][N][N], N = ib200_kform_dof_count, block (a, b) over the
+ * component spaces in component order = compute_mass_matrix(space_b, space_a, smap) with the determinant weight
+ * (src/python/mass_matrices.c:264-335 non-matching-space branch; DoF layout src/basis/de_rham_sequence.h:66-110).  The
+ * reference has no such function -- a caller loops over the blocks -- so this is the batched form of that
+ * loop.  Bilinear quads in the plane (every BASELINE configuration) take ONE launch of the Kronecker kernel; other
+ * elements one mapped mass launch per block plus a strided device copy. */
+IB200_API int ib200_kform_mass_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, unsigned k,
+                                            const integration_spec_t *rules, unsigned n_phys,
+                                            const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,
+                                            double *out, int where);
+
 /* ---- A12 (K3): batched L2-projection right-hand sides -------------------------------------- */
 /* projection_l2_dual, python/interplib/integration.py:106-168 (+ _prepare_integration :44-67):
  *   out[e][i] = sum_q fvals[e][q] * W[q] * det[e][q] * Phi[q][i]
@@ -340,10 +358,20 @@ IB200_API int ib200_l2_system_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, cons
 IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_elements, double *mass, double *rhs,
                                     int where);
 
+/* Host tables of the fast-diagonalisation projection (csrc/fastdiag.c): with A[j][i] = sum_q w_q B_j(x_q) B_i(x_q) and
+ * X[j][i] = sum_q w_q x_q B_j(x_q) B_i(x_q) of the 1-D basis under the 1-D rule, V[n][n] and lambda[n] satisfy V^T A V = I,
+ * V^T X V = diag(lambda); Vw[n][m] = w_q sum_j V[j][i] B_j(x_q).  On an element whose Jacobian determinant is
+ * alpha + beta xi0 + gamma xi1 (every bilinear quad) the inverse mass matrix of the tensor-product space is
+ * (V0 (x) V1) diag(1 / (alpha + beta lambda0_i + gamma lambda1_j)) (V0 (x) V1)^T.  INTERP_ERROR_BAD_SYSTEM when A is not
+ * positive definite (rule with fewer points than basis functions). */
+IB200_API int ib200_fastdiag_tables(basis_spec_t basis, integration_spec_t rule, double *V, double *lambda, double *Vw);
+
 /* The whole projection_l2_primal of a batch in one call (python/interplib/integration.py:171-223: dual projection, mass
- * matrix, np.linalg.solve): geometry + f samples in, primal[E][N] out.  The mass matrices are assembled into the context's
- * scratch, solved there (Cholesky) and never leave the device: a HOST call moves 8(n_phys*N_geom + Q) bytes in and 8 N
- * bytes out per element instead of the 8 N^2 of ib200_l2_system_mapped_batch. */
+ * matrix, np.linalg.solve): geometry + f samples in, primal[E][N] out.  Bilinear quads (2-D, order-1 geometry basis, square
+ * space) are projected by fast diagonalisation -- no mass matrix exists anywhere (kernels_fastdiag.cu,
+ * ib200_ctx_set_fastdiag); for every other element the mass matrices are assembled into the context's scratch, solved
+ * there (signed Cholesky) and never leave the device.  A HOST call moves 8(n_phys*N_geom + Q) bytes in and 8 N bytes out
+ * per element instead of the 8 N^2 of ib200_l2_system_mapped_batch. */
 IB200_API int ib200_l2_project_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis,
                                             const integration_spec_t *rules, unsigned n_phys,
                                             const basis_spec_t *geom_basis, size_t n_elements, const double *geom_dofs,

@@ -96,6 +96,8 @@ _PROTOTYPES = {
     "ib200_ctx_set_force_generic": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_mma_min_points": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_lo_kernel": (C.c_int, [C.c_void_p, C.c_int]),
+    "ib200_ctx_set_fastdiag": (C.c_int, [C.c_void_p, C.c_int]),
+    "ib200_ctx_set_kron": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_chunk_elements": (C.c_int, [C.c_void_p, C.c_size_t]),
     "ib200_device_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "ib200_device_free": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -122,6 +124,7 @@ _PROTOTYPES = {
          C.POINTER(C.c_uint), C.c_void_p, C.c_int],
     ),
     "ib200_incidence_matrix": (C.c_int, [BasisSpec, C.c_void_p]),
+    "ib200_fastdiag_tables": (C.c_int, [BasisSpec, IntegrationSpec, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ib200_dof_derivative_batch": (
         C.c_int,
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int],
@@ -167,6 +170,11 @@ _PROTOTYPES = {
         C.c_int,
         [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
          C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int],
+    ),
+    "ib200_kform_mass_mapped_batch": (
+        C.c_int,
+        [C.c_void_p, C.c_uint, C.POINTER(BasisSpec), C.c_uint, C.POINTER(IntegrationSpec), C.c_uint, C.POINTER(BasisSpec),
+         C.c_size_t, C.c_void_p, C.c_void_p, C.c_int],
     ),
     "ib200_l2_project_mapped_batch": (
         C.c_int,

@@ -137,6 +137,14 @@ class Context:
         """Compile-time specialised low-order mass kernel on/off (testing aid)."""
         check(lib.ib200_ctx_set_lo_kernel(self.handle, int(bool(on))))
 
+    def set_kron(self, on: bool) -> None:
+        """Kronecker-sum mass kernel for bilinear quads on/off (off: the sum-factorised DFMA / DMMA kernels)."""
+        check(lib.ib200_ctx_set_kron(self.handle, int(bool(on))))
+
+    def set_fastdiag(self, on: bool) -> None:
+        """Fast-diagonalisation projection of bilinear quads on/off (off: every mass matrix is assembled and factorised)."""
+        check(lib.ib200_ctx_set_fastdiag(self.handle, int(bool(on))))
+
     def set_chunk_elements(self, n: int) -> None:
         check(lib.ib200_ctx_set_chunk_elements(self.handle, int(n)))
 
@@ -324,6 +332,21 @@ class Context:
                                                where))
         return mass, rhs
 
+    # -- N4 + K2 -----------------------------------------------------------------------------------
+    def kform_mass_mapped(self, basis, k, rules, geom_basis, geom_dofs, n_phys, n_dofs, out=None, where=HOST, n_elements=None):
+        """The whole k-form element mass matrix M[E][N][N] (N = n_dofs = kform_dof_count): block (a, b) over the component
+        spaces = compute_mass_matrix(space_b, space_a, smap); one launch for bilinear quads   (ib200_kform_mass_mapped_batch)"""
+        Ng = _n_basis(geom_basis)
+        if where == HOST:
+            geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
+            E = geom_dofs.shape[0]
+            out = _as_out(out, (E, n_dofs, n_dofs))
+        else:
+            E = int(n_elements)
+        check(lib.ib200_kform_mass_mapped_batch(self.handle, len(rules), basis_specs(basis), int(k), rule_specs(rules), n_phys,
+                                                basis_specs(geom_basis), E, _ptr(geom_dofs), _ptr(out), where))
+        return out
+
     # -- N1 ----------------------------------------------------------------------------------------
     def l2_project_mapped(self, basis, rules, geom_basis, geom_dofs, n_phys, fvals, out=None, where=HOST, n_elements=None):
         """projection_l2_primal of a whole batch: geometry + f samples -> primal DoFs u[E][N]; the mass matrices stay in
@@ -421,6 +444,17 @@ def incidence_matrix(basis):
     out = np.empty((max(bo, 0), bo + 1))
     check(lib.ib200_incidence_matrix(basis_specs([basis])[0], out.ctypes.data_as(C.c_void_p)))
     return out
+
+
+def fastdiag_tables(basis, rule):
+    """(V[n][n], lambda[n], Vw[n][m]) of a 1-D basis under a 1-D rule: V^T A V = I, V^T X V = diag(lambda) for the mass
+    matrix A and the coordinate-weighted mass matrix X (ib200_fastdiag_tables; the tables of the fast-diagonalisation
+    projection, csrc/fastdiag.c)."""
+    n, m = basis[1] + 1, rule[1] + 1
+    V, lam, Vw = np.empty((n, n)), np.empty(n), np.empty((n, m))
+    check(lib.ib200_fastdiag_tables(basis_specs([basis])[0], rule_specs([rule])[0], V.ctypes.data_as(C.c_void_p),
+                                    lam.ctypes.data_as(C.c_void_p), Vw.ctypes.data_as(C.c_void_p)))
+    return V, lam, Vw
 
 
 def integration_space_weights(rules):

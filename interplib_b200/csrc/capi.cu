@@ -260,6 +260,10 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
         ctx->mma_min_points = std::atoi(env) <= 0 ? (1 << 30) : std::atoi(env);
     if (const char *env = std::getenv("IB200_NO_LO_KERNEL"))
         ctx->lo_kernel = std::atoi(env) == 0;
+    if (const char *env = std::getenv("IB200_NO_FASTDIAG"))
+        ctx->fastdiag = std::atoi(env) == 0;
+    if (const char *env = std::getenv("IB200_NO_KRON"))
+        ctx->kron = std::atoi(env) == 0;
     IB_CUDA(cudaSetDevice(device));
     IB_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
     if (ctx->prop.major < 10)
@@ -413,6 +417,20 @@ extern "C" int ib200_ctx_set_lo_kernel(ib200_ctx_t *ctx, int on)
 {
     IB_TRY(ctx_check(ctx));
     ctx->lo_kernel = on != 0;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_kron(ib200_ctx_t *ctx, int on)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->kron = on != 0;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_fastdiag(ib200_ctx_t *ctx, int on)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->fastdiag = on != 0;
     return INTERP_SUCCESS;
 }
 
@@ -1063,6 +1081,20 @@ extern "C" int ib200_reconstruct_points_batch(ib200_ctx_t *ctx, unsigned ndim, c
     });
 }
 
+// ---- N1: fast-diagonalisation tables (host) --------------------------------------------------------------------
+extern "C" int ib200_fastdiag_tables(basis_spec_t basis, integration_spec_t rule, double *V, double *lambda, double *Vw)
+{
+    if (!V || !lambda || !Vw)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "V/lambda/Vw must not be NULL");
+    const int res = ib200_tables_fastdiag(basis, rule, V, lambda, Vw);
+    if (res == INTERP_ERROR_BAD_SYSTEM)
+        return ib200_fail(res, "the 1-D mass matrix of basis (%d, %u) under rule (%d, %u) is not positive definite", (int)basis.type,
+                          basis.order, (int)rule.type, rule.order);
+    if (res != INTERP_SUCCESS)
+        return ib200_fail(res, "fast-diagonalisation tables: invalid basis (%d) or rule (%d) type", (int)basis.type, (int)rule.type);
+    return INTERP_SUCCESS;
+}
+
 // ---- N3: incidence / derivative DoFs ------------------------------------------------------------------------
 extern "C" int ib200_incidence_matrix(basis_spec_t basis, double *out)
 {
@@ -1219,6 +1251,90 @@ extern "C" int ib200_mass_matrix_batch(ib200_ctx_t *ctx, unsigned ndim, const ba
                        });
 }
 
+// One mapped mass-matrix operation (spaces, rule, geometry basis, weight component) prepared for launching on device
+// pointers: shared by ib200_mass_matrix_mapped_batch and the block-by-block path of ib200_kform_mass_mapped_batch.
+struct MappedMassOp
+{
+    unsigned ndim = 0, n_phys = 0;
+    const basis_spec_t *basis_in = nullptr, *basis_out = nullptr, *geom_basis = nullptr;
+    const integration_spec_t *rules = nullptr;
+    OpDesc op, gop;
+    OpHost host, ghost;
+    bool symmetric = false, match0 = false, match1 = false, fuse_geometry = false;
+    int deriv = -1, idx_out = 0;
+    std::string key_fused, key_w, key_kron;
+};
+
+static int mapped_mass_prepare(ib200_ctx *ctx, unsigned ndim, const basis_spec_t *basis_in, const basis_spec_t *basis_out,
+                               const integration_spec_t *rules, unsigned n_phys, const basis_spec_t *geom_basis, int idx_in,
+                               int idx_out, MappedMassOp *m)
+{
+    m->ndim = ndim;
+    m->n_phys = n_phys;
+    m->basis_in = basis_in;
+    m->basis_out = basis_out;
+    m->geom_basis = geom_basis;
+    m->rules = rules;
+    IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &m->op, &m->host));
+    IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &m->gop, &m->ghost));
+    m->symmetric = spaces_match(ndim, basis_in, basis_out);
+    m->deriv = idx_in < 0 ? -1 : idx_in;
+    m->idx_out = idx_out;
+    m->match0 = spaces_match(1, basis_in, basis_out);
+    m->match1 = ndim > 1 && spaces_match(1, basis_in + 1, basis_out + 1);
+    // bilinear quads in the plane: the geometry prologue is fused into the mass kernel (no [E][Q] weight array)
+    m->fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
+    m->key_fused = plan_key("massg", ndim, basis_in, basis_out, rules, geom_basis, m->deriv, 2, m->deriv, idx_out);
+    m->key_w = plan_key("mass", ndim, basis_in, basis_out, rules, nullptr, m->deriv, 1, -1, 0);
+    m->key_kron = plan_key("kron", ndim, basis_in, basis_out, rules, geom_basis, -1, 2, -1, 0);
+    return INTERP_SUCCESS;
+}
+
+// Determinant-weighted mass matrices of bilinear quads: the compile-time specialised low-order kernel where it covers the
+// shape (it sits on the write roofline), else the Kronecker kernel (two FP64 operations per entry, kernels_mass2d_kron.cu),
+// else IB200_ERROR_UNSUPPORTED and the caller's sum-factorised candidates.
+static int launch_mass2d_bilinear(ib200_ctx *ctx, const LaunchCfg &cfg, const MappedMassOp &m, size_t cnt, const double *geom,
+                                  double *out)
+{
+    if (!m.fuse_geometry || m.deriv >= 0)
+        return IB200_ERROR_UNSUPPORTED;
+    if (ctx->lo_kernel)
+    {
+        const int res = launch_mass2d_lo(ctx, cfg, m.key_fused, m.op, m.host, m.match0, m.match1, -1, 2, &m.ghost, -1, cnt, geom, out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
+    if (ctx->kron)
+        return launch_mass2d_kron(ctx, cfg, m.key_kron, 1, m.basis_out, 1, m.basis_in, m.rules, m.geom_basis, cnt, geom, out);
+    return IB200_ERROR_UNSUPPORTED;
+}
+
+// geom[cnt][n_phys][N_g] -> out[cnt][N_out][N_in] on device pointers; wscratch[cnt][Q] is used by the two-pass paths only
+static int mapped_mass_launch(ib200_ctx *ctx, const LaunchCfg &cfg, const MappedMassOp &m, size_t cnt, const double *geom, double *out,
+                              double *wscratch)
+{
+    if (!cnt)
+        return INTERP_SUCCESS;
+    if (!cfg.force_generic && m.fuse_geometry)
+    {
+        int res = launch_mass2d_bilinear(ctx, cfg, m, cnt, geom, out);
+        if (res == IB200_ERROR_UNSUPPORTED)
+            res = launch_mass2d_best(ctx, cfg, m.key_fused, m.op, m.host, m.match0, m.match1, m.deriv, 2, &m.ghost, m.deriv, m.idx_out,
+                                     cnt, geom, out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
+    IB_TRY(launch_geometry_generic(cfg, m.gop, m.n_phys, cnt, geom, nullptr, nullptr, nullptr, wscratch, m.deriv, m.idx_out));
+    if (!cfg.force_generic)
+    {
+        const int res = launch_mass2d_best(ctx, cfg, m.key_w, m.op, m.host, m.match0, m.match1, m.deriv, 1, nullptr, -1, 0, cnt, wscratch,
+                                           out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
+    return launch_mass_generic(cfg, m.op, m.symmetric, cnt, wscratch, m.deriv, out);
+}
+
 extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis_in,
                                               const basis_spec_t *basis_out, const integration_spec_t *rules,
                                               unsigned n_phys, const basis_spec_t *geom_basis, size_t n_elements,
@@ -1237,41 +1353,112 @@ extern "C" int ib200_mass_matrix_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, c
     if (idx_in >= 0 && (idx_out < 0 || idx_out >= (int)n_phys))
         return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "Index %d out of bounds for output space with %u dimensions.", idx_out,
                           n_phys);
-    OpDesc op, gop;
-    OpHost host, ghost;
-    IB_TRY(ctx_make_op(ctx, ndim, basis_in, basis_out, rules, &op, &host));
+    MappedMassOp m;
+    IB_TRY(mapped_mass_prepare(ctx, ndim, basis_in, basis_out, rules, n_phys, geom_basis, idx_in, idx_out, &m));
+    std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * m.gop.N_in},
+                                      {ARR_OUT, out, sizeof(double) * m.op.N_out * m.op.N_in},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * m.op.Q}}; // per-point weights of the two-pass paths
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        return mapped_mass_launch(ctx, cfg, m, cnt, (const double *)dev[0], (double *)dev[1], (double *)dev[2]);
+    });
+}
+
+// ---- N4 + K2: the whole k-form element mass matrix -----------------------------------------------------------------
+// out[e] = [M_ab] over the component spaces of the k-form in component order, M_ab = compute_mass_matrix(space_b, space_a,
+// smap) with the determinant weight (the blocks the reference pins).  Bilinear quads: ONE launch of the Kronecker
+// kernel writes the [N][N] matrix; everything else: one mapped mass launch per block into scratch + a strided device copy.
+extern "C" int ib200_kform_mass_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *basis, unsigned k,
+                                             const integration_spec_t *rules, unsigned n_phys, const basis_spec_t *geom_basis,
+                                             size_t n_elements, const double *geom_dofs, double *out, int where)
+{
+    IB_TRY(ctx_check(ctx));
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    NvtxRange nvtx("ib200_kform_mass_mapped_batch");
+    IB_TRY(check_geometry_dims(ndim, n_phys));
+    if (!basis || !rules || !geom_basis)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "basis/rules/geom_basis must not be NULL");
+    if (k > ndim)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "a %u-form does not exist in %u dimensions", k, ndim);
+    if (n_elements && (!out || !geom_dofs))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "geom_dofs/out must not be NULL");
+    const unsigned n_comp = ib200_kform_component_count(ndim, k);
+    std::vector<ib200_covector_t> comps(n_comp);
+    IB_TRY(ib200_kform_components(ndim, k, comps.data()));
+    std::vector<basis_spec_t> spaces((size_t)n_comp * ndim);
+    std::vector<size_t> n_dof(n_comp), offset(n_comp + 1, 0);
+    for (unsigned c = 0; c < n_comp; ++c)
+    {
+        IB_TRY(ib200_kform_component_space(ndim, basis, comps[c], spaces.data() + (size_t)c * ndim));
+        n_dof[c] = 1;
+        for (unsigned d = 0; d < ndim; ++d)
+            n_dof[c] *= spaces[(size_t)c * ndim + d].order + 1;
+        offset[c + 1] = offset[c] + n_dof[c];
+    }
+    const size_t N = offset[n_comp];
+    OpDesc gop;
+    OpHost ghost;
     IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
-    const bool symmetric = spaces_match(ndim, basis_in, basis_out);
-    const int deriv = idx_in < 0 ? -1 : idx_in;
-    const bool match0 = spaces_match(1, basis_in, basis_out);
-    const bool match1 = ndim > 1 && spaces_match(1, basis_in + 1, basis_out + 1);
-    // bilinear quads in the plane: the geometry prologue is fused into the mass kernel (no [E][Q] weight array)
-    const bool fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
-    const std::string key_fused = plan_key("massg", ndim, basis_in, basis_out, rules, geom_basis, deriv, 2, deriv, idx_out);
-    const std::string key_w = plan_key("mass", ndim, basis_in, basis_out, rules, nullptr, deriv, 1, -1, 0);
+    size_t Q = 1;
+    for (unsigned d = 0; d < ndim; ++d)
+        Q *= rules[d].order + 1;
+
+    // one launch: bilinear quads in the plane, at most two components (every 2-D k-form)
+    if (ndim == 2 && n_phys == 2 && n_comp <= 2 && ctx->kron && !ctx->force_generic)
+    {
+        std::string key = "kformkron:" + std::to_string(k);
+        key += plan_key("", ndim, basis, nullptr, rules, geom_basis, -1, 2, -1, 0);
+        const LaunchCfg probe_cfg = make_launch_cfg(ctx, ctx->stream);
+        const int probe = launch_mass2d_kron(ctx, probe_cfg, key, (int)n_comp, spaces.data(), (int)n_comp, spaces.data(), rules, geom_basis,
+                                             0, nullptr, nullptr);
+        if (probe == INTERP_SUCCESS)
+        {
+            std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
+                                              {ARR_OUT, out, sizeof(double) * N * N}};
+            return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                if (!cnt)
+                    return INTERP_SUCCESS;
+                return launch_mass2d_kron(ctx, cfg, key, (int)n_comp, spaces.data(), (int)n_comp, spaces.data(), rules, geom_basis, cnt,
+                                          (const double *)dev[0], (double *)dev[1]);
+            });
+        }
+        if (probe != IB200_ERROR_UNSUPPORTED)
+            return probe;
+    }
+
+    // block by block
+    std::vector<MappedMassOp> ops((size_t)n_comp * n_comp);
+    size_t max_block = 0;
+    for (unsigned a = 0; a < n_comp; ++a)
+        for (unsigned b = 0; b < n_comp; ++b)
+        {
+            IB_TRY(mapped_mass_prepare(ctx, ndim, spaces.data() + (size_t)b * ndim, spaces.data() + (size_t)a * ndim, rules, n_phys,
+                                       geom_basis, -1, 0, &ops[(size_t)a * n_comp + b]));
+            max_block = std::max(max_block, n_dof[a] * n_dof[b]);
+        }
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
-                                      {ARR_OUT, out, sizeof(double) * op.N_out * op.N_in},
-                                      {ARR_SCRATCH, nullptr, sizeof(double) * op.Q}};
-    return run_batched(ctx, n_elements, arrays, where, 0,
-                       [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
-                           if (!cfg.force_generic && cnt && fuse_geometry)
-                           {
-                               const int res = launch_mass2d_best(ctx, cfg, key_fused, op, host, match0, match1, deriv, 2, &ghost,
-                                                                  deriv, idx_out, cnt, (const double *)dev[0], (double *)dev[1]);
-                               if (res != IB200_ERROR_UNSUPPORTED)
-                                   return res;
-                           }
-                           IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, (const double *)dev[0], nullptr, nullptr,
-                                                          nullptr, (double *)dev[2], deriv, idx_out));
-                           if (!cfg.force_generic && cnt)
-                           {
-                               const int res = launch_mass2d_best(ctx, cfg, key_w, op, host, match0, match1, deriv, 1, nullptr, -1,
-                                                                  0, cnt, (const double *)dev[2], (double *)dev[1]);
-                               if (res != IB200_ERROR_UNSUPPORTED)
-                                   return res;
-                           }
-                           return launch_mass_generic(cfg, op, symmetric, cnt, (const double *)dev[2], deriv, (double *)dev[1]);
-                       });
+                                      {ARR_OUT, out, sizeof(double) * N * N},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * max_block},
+                                      {ARR_SCRATCH, nullptr, sizeof(double) * Q}};
+    return run_batched(ctx, n_elements, arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+        if (!cnt)
+            return INTERP_SUCCESS;
+        for (unsigned a = 0; a < n_comp; ++a)
+            for (unsigned b = 0; b < n_comp; ++b)
+            {
+                double *block = n_comp == 1 ? (double *)dev[1] : (double *)dev[2];
+                IB_TRY(mapped_mass_launch(ctx, cfg, ops[(size_t)a * n_comp + b], cnt, (const double *)dev[0], block, (double *)dev[3]));
+                if (n_comp == 1)
+                    continue;
+                // block[e][ja][ib] -> out[e][offset_a + ja][offset_b + ib]
+                cudaMemcpy3DParms cp{};
+                cp.srcPtr = make_cudaPitchedPtr(block, n_dof[b] * sizeof(double), n_dof[b] * sizeof(double), n_dof[a]);
+                cp.dstPtr = make_cudaPitchedPtr((double *)dev[1] + offset[a] * N + offset[b], N * sizeof(double), N * sizeof(double), N);
+                cp.extent = make_cudaExtent(n_dof[b] * sizeof(double), n_dof[a], cnt);
+                cp.kind = cudaMemcpyDeviceToDevice;
+                IB_CUDA(cudaMemcpy3DAsync(&cp, cfg.stream));
+            }
+        return INTERP_SUCCESS;
+    });
 }
 
 // ---- K3 ----------------------------------------------------------------------------------------------------
@@ -1371,9 +1558,32 @@ static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *b
     IB_TRY(ctx_make_op(ctx, ndim, geom_basis, nullptr, rules, &gop, &ghost));
     const bool fuse_geometry = ndim == 2 && n_phys == 2 && geom_basis[0].order == 1 && geom_basis[1].order == 1;
     const std::string key_fused = plan_key("massg", ndim, basis, basis, rules, geom_basis, -1, 2, -1, 0);
+    const std::string key_kron = plan_key("kron", ndim, basis, basis, rules, geom_basis, -1, 2, -1, 0);
     const std::string key_w = plan_key("mass", ndim, basis, basis, rules, nullptr, -1, 1, -1, 0);
     const std::string key_l2 = plan_key("l2g", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
     const std::string key_l2w = plan_key("l2", ndim, basis, nullptr, rules, nullptr, 1, 0, 0, 0);
+    if (solve && fuse_geometry && ctx->fastdiag && !ctx->force_generic)
+    {
+        // bilinear quads: det J is linear in the reference coordinates, so M^-1 is two 1-D transforms and a diagonal
+        // scaling (kernels_fastdiag.cu) -- no mass matrix, no factorisation, no scratch
+        const std::string key_fd = plan_key("l2fd", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
+        const LaunchCfg probe_cfg = make_launch_cfg(ctx, ctx->stream);
+        const int probe = launch_l2proj_fd2d(ctx, probe_cfg, key_fd, basis, rules, geom_basis, 0, nullptr, nullptr, nullptr);
+        if (probe == INTERP_SUCCESS)
+        {
+            std::vector<BatchArray> fd_arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
+                                                 {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
+                                                 {ARR_OUT, rhs, sizeof(double) * op.N_in}};
+            return run_batched(ctx, n_elements, fd_arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                if (!cnt)
+                    return INTERP_SUCCESS;
+                return launch_l2proj_fd2d(ctx, cfg, key_fd, basis, rules, geom_basis, cnt, (const double *)dev[1],
+                                          (const double *)dev[0], (double *)dev[2]);
+            });
+        }
+        if (probe != IB200_ERROR_UNSUPPORTED)
+            return probe;
+    }
     std::vector<BatchArray> arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * n_phys * gop.N_in},
                                       {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
                                       {solve ? ARR_SCRATCH : ARR_OUT, solve ? nullptr : mass, sizeof(double) * op.N_out * op.N_in},
@@ -1390,9 +1600,22 @@ static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *b
                                    if (res != IB200_ERROR_UNSUPPORTED)
                                        return res;
                                }
-                               int res = launch_mass2d_best(ctx, cfg, key_fused, op, host, true, true, -1, 2, &ghost, -1, 0, cnt, g, M);
+                               int res = ctx->kron ? launch_mass2d_kron(ctx, cfg, key_kron, 1, basis, 1, basis, rules, geom_basis, cnt, g, M)
+                                                   : (int)IB200_ERROR_UNSUPPORTED;
+                               if (res == IB200_ERROR_UNSUPPORTED)
+                                   res = launch_mass2d_best(ctx, cfg, key_fused, op, host, true, true, -1, 2, &ghost, -1, 0, cnt, g, M);
                                if (res == INTERP_SUCCESS)
+                               {
+                                   // M is done; the right-hand side by the same chain as ib200_l2_dual_mapped_batch
                                    res = launch_l2dual2d_fast(ctx, cfg, key_l2, op, host, 2, &ghost, cnt, f, g, b);
+                                   if (res != IB200_ERROR_UNSUPPORTED)
+                                       return res;
+                                   IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, g, nullptr, nullptr, nullptr, w, -1, 0));
+                                   res = launch_l2dual2d_fast(ctx, cfg, key_l2w, op, host, 1, nullptr, cnt, f, w, b);
+                                   if (res == IB200_ERROR_UNSUPPORTED)
+                                       res = launch_l2_generic(cfg, op, cnt, f, w, b);
+                                   return res;
+                               }
                                if (res != IB200_ERROR_UNSUPPORTED)
                                    return res;
                            }

@@ -118,6 +118,8 @@ struct ib200_ctx
     bool force_generic = false;
     int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
     bool lo_kernel = true;   // compile-time specialised low-order mass kernel (IB200_NO_LO_KERNEL=1 disables it)
+    bool kron = true;        // Kronecker-sum mass kernel for bilinear quads (IB200_NO_KRON=1: sum-factorised kernels only)
+    bool fastdiag = true;    // primal projections of bilinear quads by fast diagonalisation (IB200_NO_FASTDIAG=1: factorise M)
     size_t chunk_elements = 0;
     // staging (host-pointer calls) and scratch (fused generic path)
     void *stage_dev[3] = {nullptr, nullptr, nullptr};
@@ -207,6 +209,12 @@ int launch_mass2d_lo(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &ke
                      const double *wsrc, double *out, const double *fvals = nullptr, double *rhs = nullptr);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);
+int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, int n_row_groups, const basis_spec_t *rows,
+                       int n_col_groups, const basis_spec_t *cols, const integration_spec_t *rules, const basis_spec_t *geom_basis,
+                       size_t E, const double *geom, double *out);
+int launch_l2proj_fd2d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const basis_spec_t *basis,
+                       const integration_spec_t *rules, const basis_spec_t *geom_basis, size_t E, const double *fvals,
+                       const double *geom, double *out);
 
 // ---- dynamic tile scheduling (device side) ----------------------------------------------------------------------
 // sched[0] = next unclaimed work item, sched[1] = participants that have finished.  SMs (and, for warp-autonomous

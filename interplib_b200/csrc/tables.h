@@ -27,6 +27,10 @@ int ib200_tables_gauss_lobatto(unsigned order, unsigned max_iter, double tol, do
                                int *non_converged);
 int ib200_tables_bernstein_samples(unsigned order, size_t cnt, const double *t, double *out);
 int ib200_tables_bernstein_from_power(unsigned n, double *c);
+/* fastdiag.c */
+int ib200_tables_fastdiag(basis_spec_t basis, integration_spec_t rule, double *V, double *lambda, double *Vw);
+int ib200_tables_linear_basis(basis_spec_t basis, double a[2], double s[2]);
+int ib200_tables_pair_moments(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, double *A, double *X);
 
 #ifdef __cplusplus
 }

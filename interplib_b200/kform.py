@@ -159,6 +159,12 @@ def kform_mass_blocks(ctx, basis, k: int, rules, geom_basis, geom_dofs, n_phys: 
             for a, sa in enumerate(spaces) for b, sb in enumerate(spaces)}
 
 
+def kform_mass_matrix(ctx, basis, k: int, rules, geom_basis, geom_dofs, n_phys: int, **kw):
+    """The k-form element mass matrices M[E][N][N] in one call (one GPU launch for bilinear quads in the plane); block
+    (a, b) of M[e] is what kform_mass_blocks returns under (a, b)."""
+    return ctx.kform_mass_mapped(basis, k, rules, geom_basis, geom_dofs, n_phys, kform_dof_count(basis, k), **kw)
+
+
 def assemble_blocks(blocks: dict) -> np.ndarray:
     """Host-side layout of {(a, b): [E][N_a][N_b]} into one [E][N][N] element matrix (N = kform_dof_count)."""
     n = 1 + max(a for a, _ in blocks)
