@@ -516,25 +516,31 @@ class Runner:
             return d_g, d_f
 
         d_all = ctx.alloc(total_elements * N * 8)      # the gathered [E][25] primal DoFs, every rank
-        n_sub = 4                                       # sub-slabs per rank: the gather of one overlaps the compute of the next
+        # gather destination registered with the communicator: slabs travel as copy-engine pushes into the peers' IPC-mapped
+        # buffers (NVLink) instead of NCCL kernels; False -> NCCL broadcasts ($IB200_NO_P2P_GATHER=1 forces that)
+        p2p = comm.register_gather(d_all, total_elements * N * 8)
+        n_sub = 4                                       # sub-slabs per rank: the gather of one overlaps the assembly of the same and the next
         sub = -(-part.max_count // n_sub)
         d_norm = ctx.alloc(8 * n_sub)
 
-        def job(d_g, d_f, d_b, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub):
-            """Projection of `count` elements starting at global element `first` (this rank's slab, or everything for the
-            single-rank reference), pipelined in n_sub sub-slabs."""
+        def job(d_g, d_f, d_b, d_M, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub):
+            """Mass matrices + L2 projection of `count` elements starting at global element `first` (this rank's block, or all
+            of them for the single-rank reference), pipelined in n_sub sub-slabs: primal DoFs first (fast diagonalisation),
+            their all-gather goes to the communicator's stream, the (M, b) assembly and the norm run meanwhile."""
             for k in range(n_sub):
                 lo, hi = min(count, k * sub), min(count, (k + 1) * sub)
+                g, f = int(d_g) + lo * 64, int(d_f) + lo * Q * 8
+                u = int(d_all) + (first + lo) * N * 8
+                b = int(d_b) + lo * N * 8
+                M = int(d_M) + lo * N * N * 8
                 if hi > lo and compute:
-                    g, f = int(d_g) + lo * 64, int(d_f) + lo * Q * 8
-                    u = int(d_all) + (first + lo) * N * 8
-                    b = int(d_b) + lo * N * 8
-                    ctx.l2_dual_mapped(basis, rules, gb, g, cfg.n_phys, f, out=b, where=DEVICE, n_elements=hi - lo)
                     ctx.l2_project_mapped(basis, rules, gb, g, cfg.n_phys, f, out=u, where=DEVICE, n_elements=hi - lo)
-                    ctx.dot(b, u, out=int(d_norm) + 8 * k, where=DEVICE, n=(hi - lo) * N)
                 if collectives:
                     counts, offsets = part.slab_layout(N, k * sub, sub)
                     comm.allgatherv(int(d_all) + (part.first + min(part.count, k * sub)) * N * 8, d_all, counts, offsets, overlap=True)
+                if hi > lo and compute:
+                    ctx.l2_system_mapped(basis, rules, gb, g, cfg.n_phys, f, mass=M, rhs=b, where=DEVICE, n_elements=hi - lo)
+                    ctx.dot(b, u, out=int(d_norm) + 8 * k, where=DEVICE, n=(hi - lo) * N)
             if collectives:
                 comm.allreduce_sums(int(d_norm), n_sub)
                 comm.join()
@@ -550,14 +556,15 @@ class Runner:
 
         d_g, d_f = upload_inputs(part.first, part.count)
         d_b = ctx.alloc(max(part.count, 1) * N * 8)
-        run_all = lambda: job(d_g, d_f, d_b, part.first, part.count, True)  # noqa: E731
+        d_M = ctx.alloc(max(part.count, 1) * N * N * 8)   # this rank's element mass matrices: stay sharded, never gathered
+        run_all = lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True)  # noqa: E731
         for _ in range(max(warmup, 3)):
             run_all()
         launches0 = ctx.stats()["kernel_launches"]
         ms_step = timed(run_all, steps)
         launches = ctx.stats()["kernel_launches"] - launches0
-        ms_compute = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, False), steps)
-        ms_coll = timed(lambda: job(d_g, d_f, d_b, part.first, part.count, True, compute=False), steps)
+        ms_compute = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, False), steps)
+        ms_coll = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True, compute=False), steps)
         comm.check()
 
         # ---- parity of the collective: a 4096-element slab owned by the LAST rank, recomputed by this rank alone, must equal
@@ -575,7 +582,7 @@ class Runner:
         got = d_all.download((chk_n, N), offset_bytes=chk_first * N * 8)
         parity_local = bool(np.array_equal(mine, got)) and bool(np.isfinite(got).all())
         parity = self.max_over_ranks(0.0 if parity_local else 1.0) == 0.0
-        for b in (c_g, c_f, c_u, d_g, d_f, d_b):
+        for b in (c_g, c_f, c_u, d_g, d_f, d_b, d_M):
             b.free()
 
         # ---- the same 2^24 elements on ONE GPU (rank 0 alone, no collective): the denominator of the strong-scaling efficiency
@@ -584,7 +591,8 @@ class Runner:
             if rank == 0:
                 s_g, s_f = upload_inputs(0, total_elements)
                 s_b = ctx.alloc(total_elements * N * 8)
-                one = lambda: job(s_g, s_f, s_b, 0, total_elements, False, sub=-(-total_elements // n_sub))  # noqa: E731
+                s_M = ctx.alloc(total_elements * N * N * 8)
+                one = lambda: job(s_g, s_f, s_b, s_M, 0, total_elements, False, sub=-(-total_elements // n_sub))  # noqa: E731
                 for _ in range(2):
                     one()
                 ctx.synchronize()
@@ -594,36 +602,50 @@ class Runner:
                     one()
                 ctx.timer_stop(3)
                 ms_single = ctx.timer_ms(3) / k1
-                for b in (s_g, s_f, s_b):
+                for b in (s_g, s_f, s_b, s_M):
                     b.free()
             self.barrier()
             ms_single = self.max_over_ranks(ms_single or 0.0)
         else:
             ms_single = ms_compute
         nccl = comm.info()["nccl_version"]
+        comm.unregister_gather()
         comm.close()
         d_all.free()
         d_norm.free()
         gather_bytes_in = (total_elements - part.max_count) * N * 8  # bytes every GPU receives
+        link_bound_ms = gather_bytes_in / 900e9 * 1e3
+        # algorithmic bytes of the whole job per element: geometry + f in, M + b + u out (SURVEY 8d C5 row + the primal DoFs)
+        job_bytes = 8 * (8 + Q + N * N + 2 * N)
         rec = {
-            "metric": "l2_projections_per_s", "unit": "elements/s", "scaling": "strong",
+            "metric": "mass_matrix_and_l2_projection_per_s", "unit": "elements/s", "scaling": "strong",
             "value": total_elements / (ms_step * 1e-3), "ms_per_step": ms_step, "steps": steps,
             "config": {"workload": f"c5: {cfg.description}", "total_elements": total_elements, "elements_per_gpu": part.max_count,
                        "basis": [list(b) for b in cfg.basis], "rule": [list(r) for r in cfg.rules],
-                       "step": "per rank: L2 right-hand sides + fused mass-matrix assembly and solve (ib200_l2_project_mapped_batch) + "
-                               "b.u norm of its block of the 16M quads; then NCCL all-gather of the [E,25] primal DoFs to every rank and "
-                               "all-reduce of the norms, issued through the C ABI, all inside the CUDA-event region",
-                       "pipeline": f"{n_sub} sub-slabs per rank; the all-gather of sub-slab k runs on the communicator's stream "
-                                   "while sub-slab k+1 is computed",
-                       "parallelism": f"element block partition x{world}, NCCL {nccl} all-gather + all-reduce"},
+                       "step": "per rank, for its block of the 16M quads: primal DoFs u (ib200_l2_project_mapped_batch, fast "
+                               "diagonalisation), element mass matrices M + right-hand sides b (ib200_l2_system_mapped_batch; M stays "
+                               "resident and sharded, 5 000 B per element), norm b.u (ib200_dot); then NCCL all-gather of the [E,25] primal "
+                               "DoFs to every rank and all-reduce of the norms, issued through the C ABI, all inside the CUDA-event region",
+                       "pipeline": f"{n_sub} sub-slabs per rank; the all-gather of a sub-slab's DoFs runs on the communicator's "
+                                   "(high-priority) stream while its mass matrices and the next sub-slab are computed",
+                       "parallelism": f"element block partition x{world}, NCCL {nccl} all-gather + all-reduce",
+                       "gather_path": ("copy-engine pushes into IPC-mapped peer buffers over NVLink (ib200_comm_register_gather), arrival "
+                                       "published by a one-double NCCL all-reduce") if p2p else "NCCL broadcasts grouped per sub-slab"},
             "compute_only_ms": ms_compute, "collective_only_ms": ms_coll, "exposed_collective_ms": ms_step - ms_compute,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_element": job_bytes,
+                         "achieved": job_bytes * part.max_count / (ms_compute * 1e-3) / 1e9, "peak": self.hbm_peak, "unit": "GB/s",
+                         "frac": job_bytes * part.max_count / (ms_compute * 1e-3) / 1e9 / self.hbm_peak,
+                         "note": "compute-only pass of one rank (no collective): three launches per sub-slab"},
             "collective": {"allgather_bytes_received_per_gpu": gather_bytes_in,
                            "allgather_gbs_per_gpu": (gather_bytes_in / (ms_coll * 1e-3) / 1e9) if ms_coll > 0 and world > 1 else None,
                            "link_peak_gbs_per_direction": 900.0,
-                           "link_bound_ms": gather_bytes_in / 900e9 * 1e3},
+                           "link_bound_ms": link_bound_ms},
             "single_gpu_ms": ms_single, "speedup_vs_single_gpu": ms_single / ms_step,
             "efficiency": ms_single / ms_step / world,
             "compute_efficiency": ms_single / ms_compute / world,
+            # what NVLink's 900 GB/s into every GPU allows for this job: the gathered DoFs (3.4 GB on every rank) cannot arrive
+            # faster than link_bound_ms, however well the transfer hides behind the kernels
+            "link_bound_efficiency": ms_single / max(ms_single / world, link_bound_ms) / world,
             "collective_parity": parity, "projection_norm_sq": proj_sq, "gpu_launches": int(launches) * world,
         }
         return rec

@@ -418,6 +418,14 @@ IB200_API int ib200_allgather_slabs(ib200_comm_t *comm, const double *local, siz
 IB200_API int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *out, const size_t *counts,
                                const size_t *offsets, int on_side_stream);
 IB200_API int ib200_comm_join(ib200_comm_t *comm);
+/* Collective.  Registers `out` (the BASE of an ib200_alloc / cudaMalloc allocation of `bytes` bytes, the same size on every
+ * rank) as gather destination: the ranks exchange CUDA IPC handles and map each other's buffers.  From then on
+ * ib200_allgatherv / ib200_allgather_slabs with this `out` push the local slab straight into the peers' buffers -- one
+ * copy-engine transfer per peer over NVLink, no SM, no staging, no NCCL kernel -- and the arrival is published by a
+ * one-double all-reduce (inside ib200_comm_join for side-stream calls).  IB200_ERROR_UNSUPPORTED, on every rank alike and
+ * without error text, when IPC mapping is unavailable or $IB200_NO_P2P_GATHER is set: the NCCL path keeps serving. */
+IB200_API int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_t bytes);
+IB200_API int ib200_comm_unregister_gather(ib200_comm_t *comm);
 /* in-place all-reduce(sum) of n doubles in device memory (projection norms) */
 IB200_API int ib200_allreduce_sums(ib200_comm_t *comm, double *values, size_t n);
 

@@ -196,6 +196,8 @@ _PROTOTYPES = {
     "ib200_allgather_slabs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]),
     "ib200_allgatherv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.c_int]),
     "ib200_comm_join": (C.c_int, [C.c_void_p]),
+    "ib200_comm_register_gather": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "ib200_comm_unregister_gather": (C.c_int, [C.c_void_p]),
     "ib200_allreduce_sums": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
 }
 

@@ -103,6 +103,15 @@ struct ib200_comm
     cudaStream_t side = nullptr; // stream of overlapped collectives
     cudaEvent_t fork = nullptr, join = nullptr;
     bool side_busy = false;
+    // registered gather destination (ib200_comm_register_gather): the peers' buffers mapped through CUDA IPC, one push
+    // stream + event per peer, a flag for the arrival barrier
+    double *reg_out = nullptr;
+    size_t reg_bytes = 0;
+    std::vector<double *> peer;
+    std::vector<cudaStream_t> push;
+    std::vector<cudaEvent_t> pushed;
+    double *flag = nullptr;
+    bool p2p_pending_side = false;
 };
 
 namespace
@@ -179,7 +188,11 @@ extern "C" int ib200_comm_create(ib200_ctx_t *ctx, int n_ranks, int rank, const 
         delete comm;
         return nccl_fail(nullptr, res, "ncclCommInitRank");
     }
-    if (cudaStreamCreateWithFlags(&comm->side, cudaStreamNonBlocking) != cudaSuccess ||
+    // the side stream outranks the compute stream: the persistent compute kernels fill every SM, and a collective queued
+    // behind them would otherwise only get CTAs once a whole compute launch has drained
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&comm->side, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
         cudaEventCreateWithFlags(&comm->fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&comm->join, cudaEventDisableTiming) != cudaSuccess)
     {
@@ -196,6 +209,7 @@ extern "C" int ib200_comm_destroy(ib200_comm_t *comm)
         return INTERP_SUCCESS;
     if (comm->ctx)
         cudaSetDevice(comm->ctx->device);
+    ib200_comm_unregister_gather(comm);
     if (comm->side)
     {
         cudaStreamSynchronize(comm->side);
@@ -265,6 +279,33 @@ extern "C" int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *
         st = comm->side;
         comm->side_busy = true;
     }
+    if (comm->reg_out && out == comm->reg_out && comm->n_ranks > 1)
+    {
+        // registered destination: push the local slab straight into every peer's buffer, one copy-engine transfer per peer
+        // on its own stream (NVLink / NVSwitch), no SM and no staging involved; arrival is published by the barrier of
+        // ib200_comm_join (side stream) or right here (compute stream)
+        const size_t bytes = counts[comm->rank] * sizeof(double);
+        if ((offsets[comm->rank] + counts[comm->rank]) * sizeof(double) > comm->reg_bytes)
+            return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "slab exceeds the registered gather buffer");
+        if (!on_side_stream)
+            IB_CUDA(cudaEventRecord(comm->fork, ctx->stream));
+        for (int r = 0; r < comm->n_ranks; ++r)
+        {
+            if (r == comm->rank || bytes == 0)
+                continue;
+            IB_CUDA(cudaStreamWaitEvent(comm->push[r], comm->fork, 0));
+            IB_CUDA(cudaMemcpyAsync(comm->peer[r] + offsets[comm->rank], send, bytes, cudaMemcpyDefault, comm->push[r]));
+            IB_CUDA(cudaEventRecord(comm->pushed[r], comm->push[r]));
+            IB_CUDA(cudaStreamWaitEvent(st, comm->pushed[r], 0));
+        }
+        if (bytes && send != out + offsets[comm->rank])
+            IB_CUDA(cudaMemcpyAsync(out + offsets[comm->rank], send, bytes, cudaMemcpyDeviceToDevice, st));
+        if (on_side_stream)
+            comm->p2p_pending_side = true;
+        else
+            IB_NCCL(comm, g_nccl.AllReduce(comm->flag, comm->flag, 1, ncclDouble, ncclSum, comm->nccl, st));
+        return INTERP_SUCCESS;
+    }
     if (even && packed)
     {
         // equal, back-to-back slabs: the library's all-gather (in place when `send` already sits at its offset)
@@ -300,12 +341,140 @@ extern "C" int ib200_allgather_slabs(ib200_comm_t *comm, const double *local, si
     return ib200_allgatherv(comm, local, out, counts.data(), offsets.data(), 0);
 }
 
+// Collective.  Maps every peer's gather destination into this process (CUDA IPC) so that ib200_allgatherv on `out` can push
+// slabs with copy engines.  `out` must be the base of a cudaMalloc allocation (ib200_alloc) of `bytes` bytes, the same size
+// on every rank.  IB200_ERROR_UNSUPPORTED (on every rank alike) when IPC mapping is not available: the caller keeps NCCL.
+extern "C" int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_t bytes)
+{
+    IB_TRY(comm_check(comm));
+    if (!out || !bytes)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "out must not be NULL");
+    IB_TRY(ib200_comm_unregister_gather(comm));
+    ib200_ctx *ctx = comm->ctx;
+    std::lock_guard<std::mutex> lock(ctx->mutex);
+    const int n = comm->n_ranks;
+    if (!comm->flag)
+    {
+        IB_CUDA(cudaMalloc((void **)&comm->flag, sizeof(double)));
+        IB_CUDA(cudaMemset(comm->flag, 0, sizeof(double)));
+    }
+    if (n == 1)
+    {
+        comm->reg_out = out;
+        comm->reg_bytes = bytes;
+        return INTERP_SUCCESS;
+    }
+    struct Slot
+    {
+        cudaIpcMemHandle_t handle;
+        unsigned long long bytes;
+        int ok;
+        int pad;
+    };
+    static_assert(sizeof(Slot) % 8 == 0, "slot size");
+    std::vector<Slot> slots(n);
+    Slot mine{};
+    mine.bytes = bytes;
+    mine.ok = (std::getenv("IB200_NO_P2P_GATHER") == nullptr && cudaIpcGetMemHandle(&mine.handle, out) == cudaSuccess) ? 1 : 0;
+    cudaGetLastError();
+    Slot *d_slots = nullptr;
+    IB_CUDA(cudaMalloc((void **)&d_slots, sizeof(Slot) * n));
+    IB_CUDA(cudaMemcpyAsync(d_slots + comm->rank, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream));
+    const ncclResult_t res = g_nccl.AllGather(d_slots + comm->rank, d_slots, sizeof(Slot), ncclChar, comm->nccl, ctx->stream);
+    if (res != ncclSuccess)
+    {
+        cudaFree(d_slots);
+        return nccl_fail(comm, res, "ncclAllGather of the IPC handles");
+    }
+    IB_CUDA(cudaMemcpyAsync(slots.data(), d_slots, sizeof(Slot) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_slots);
+    bool ok = true;
+    for (int r = 0; r < n; ++r)
+        ok = ok && slots[r].ok && slots[r].bytes == bytes;
+    comm->peer.assign(n, nullptr);
+    for (int r = 0; r < n && ok; ++r)
+    {
+        if (r == comm->rank)
+            continue;
+        void *p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, slots[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+        {
+            cudaGetLastError();
+            ok = false;
+            break;
+        }
+        comm->peer[r] = (double *)p;
+    }
+    // all ranks or none: agree on the outcome
+    double agree = ok ? 0.0 : 1.0;
+    IB_CUDA(cudaMemcpyAsync(comm->flag, &agree, sizeof agree, cudaMemcpyHostToDevice, ctx->stream));
+    IB_NCCL(comm, g_nccl.AllReduce(comm->flag, comm->flag, 1, ncclDouble, ncclSum, comm->nccl, ctx->stream));
+    IB_CUDA(cudaMemcpyAsync(&agree, comm->flag, sizeof agree, cudaMemcpyDeviceToHost, ctx->stream));
+    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    IB_CUDA(cudaMemsetAsync(comm->flag, 0, sizeof(double), ctx->stream));
+    if (agree != 0.0)
+    {
+        for (int r = 0; r < n; ++r)
+            if (comm->peer[r])
+                cudaIpcCloseMemHandle(comm->peer[r]);
+        comm->peer.clear();
+        cudaGetLastError();
+        return IB200_ERROR_UNSUPPORTED;
+    }
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    comm->push.assign(n, nullptr);
+    comm->pushed.assign(n, nullptr);
+    for (int r = 0; r < n; ++r)
+    {
+        if (r == comm->rank)
+            continue;
+        IB_CUDA(cudaStreamCreateWithPriority(&comm->push[r], cudaStreamNonBlocking, prio_hi));
+        IB_CUDA(cudaEventCreateWithFlags(&comm->pushed[r], cudaEventDisableTiming));
+    }
+    comm->reg_out = out;
+    comm->reg_bytes = bytes;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_comm_unregister_gather(ib200_comm_t *comm)
+{
+    if (!comm || !comm->ctx)
+        return INTERP_SUCCESS;
+    cudaSetDevice(comm->ctx->device);
+    for (size_t r = 0; r < comm->push.size(); ++r)
+        if (comm->push[r])
+        {
+            cudaStreamSynchronize(comm->push[r]);
+            cudaStreamDestroy(comm->push[r]);
+            cudaEventDestroy(comm->pushed[r]);
+        }
+    comm->push.clear();
+    comm->pushed.clear();
+    for (size_t r = 0; r < comm->peer.size(); ++r)
+        if (comm->peer[r])
+            cudaIpcCloseMemHandle(comm->peer[r]);
+    comm->peer.clear();
+    comm->reg_out = nullptr;
+    comm->reg_bytes = 0;
+    comm->p2p_pending_side = false;
+    return INTERP_SUCCESS;
+}
+
 extern "C" int ib200_comm_join(ib200_comm_t *comm)
 {
     IB_TRY(comm_check(comm));
     std::lock_guard<std::mutex> lock(comm->ctx->mutex);
     if (!comm->side_busy)
         return INTERP_SUCCESS;
+    if (comm->p2p_pending_side)
+    {
+        // every rank's pushes precede its entry into this all-reduce in stream order: when it completes here, the slabs
+        // of all peers have landed in this rank's buffer
+        IB_NCCL(comm, g_nccl.AllReduce(comm->flag, comm->flag, 1, ncclDouble, ncclSum, comm->nccl, comm->side));
+        comm->p2p_pending_side = false;
+    }
     IB_CUDA(cudaEventRecord(comm->join, comm->side));
     IB_CUDA(cudaStreamWaitEvent(comm->ctx->stream, comm->join, 0));
     comm->side_busy = false;

@@ -143,6 +143,19 @@ class NcclComm:
         check(lib.ib200_allgather_slabs(self.handle, C.c_void_p(int(local) if local is not None else 0), int(n_elements),
                                         int(elem_doubles), C.c_void_p(int(out))))
 
+    def register_gather(self, out, nbytes: int) -> bool:
+        """Collective: map every rank's gather destination ``out`` (base of a device allocation of ``nbytes``) into every
+        other rank (CUDA IPC); all-gathers into ``out`` then go as copy-engine pushes over NVLink instead of NCCL kernels.
+        False when peer mapping is unavailable (the NCCL path stays in use)."""
+        res = lib.ib200_comm_register_gather(self.handle, C.c_void_p(int(out)), int(nbytes))
+        if res == 103:  # IB200_ERROR_UNSUPPORTED
+            return False
+        check(res)
+        return True
+
+    def unregister_gather(self) -> None:
+        check(lib.ib200_comm_unregister_gather(self.handle))
+
     def join(self) -> None:
         """Make the context stream wait for the collectives that were sent to the side stream (``overlap=True``)."""
         check(lib.ib200_comm_join(self.handle))

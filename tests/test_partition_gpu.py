@@ -57,6 +57,23 @@ def _worker(rank: int, world: int, port: int, E: int, tmp: str):
     comm.join()
     ctx.synchronize()
     assert np.array_equal(d_all.download((E, cfg.N)), dofs)
+    # registered destination: the same pipelined gather as copy-engine pushes into IPC-mapped peer buffers (NVLink), plus a
+    # whole-slab call on the compute stream; must deliver the same bytes as NCCL did
+    d_p2p = ctx.alloc(E * cfg.N * 8)
+    p2p = comm.register_gather(d_p2p, E * cfg.N * 8)
+    assert p2p or world == 1 or os.environ.get("IB200_NO_P2P_GATHER"), "CUDA IPC peer mapping failed on a multi-GPU box"
+    for lo in range(0, part.max_count, step):
+        counts, offsets = part.slab_layout(cfg.N, lo, step)
+        comm.allgatherv(int(ctx_local) + min(lo, part.count) * cfg.N * 8, d_p2p, counts, offsets, overlap=True)
+    comm.join()
+    ctx.synchronize()
+    assert np.array_equal(d_p2p.download((E, cfg.N)), dofs)
+    d_p2p.upload(np.zeros((E, cfg.N)))
+    comm.allgather_slabs(ctx_local, E, cfg.N, d_p2p)
+    ctx.synchronize()
+    assert np.array_equal(d_p2p.download((E, cfg.N)), dofs)
+    comm.unregister_gather()
+    np.save(Path(tmp, f"p2p{rank}.npy"), np.array([1.0 if p2p else 0.0]))
     comm.check()
     np.save(Path(tmp, f"dofs{rank}.npy"), dofs)
     np.save(Path(tmp, f"norm{rank}.npy"), np.array([norms["proj_sq"]]))
