@@ -289,10 +289,11 @@ extern "C" int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *
             return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "slab exceeds the registered gather buffer");
         if (!on_side_stream)
             IB_CUDA(cudaEventRecord(comm->fork, ctx->stream));
-        for (int r = 0; r < comm->n_ranks; ++r)
+        // peers in ring order starting after this rank: at any moment the copies in flight form a permutation, no GPU is
+        // the target of all the others at once
+        for (int k = 1; k < comm->n_ranks && bytes; ++k)
         {
-            if (r == comm->rank || bytes == 0)
-                continue;
+            const int r = (comm->rank + k) % comm->n_ranks;
             IB_CUDA(cudaStreamWaitEvent(comm->push[r], comm->fork, 0));
             IB_CUDA(cudaMemcpyAsync(comm->peer[r] + offsets[comm->rank], send, bytes, cudaMemcpyDefault, comm->push[r]));
             IB_CUDA(cudaEventRecord(comm->pushed[r], comm->push[r]));
