@@ -34,7 +34,7 @@ def mapped_fvals(cfg, coords):
     return f(*[coords[:, a, 0, :] for a in range(cfg.n_phys)])
 
 
-def make(cfg, count, with_mass=True, mass_stride=1, extra=None):
+def make(cfg, count, with_mass=True, mass_stride=1, extra=None, full_mass_of=None):
     idx, geom = sample_elements(cfg, count)
     E = len(idx)
     basis, rules, gb = list(cfg.basis), list(cfg.rules), list(cfg.geom_basis)
@@ -50,6 +50,9 @@ def make(cfg, count, with_mass=True, mass_stride=1, extra=None):
         m = rd.mass(basis, basis, rules, E, gb, geom, cfg.n_phys)
         data["mass_stride"] = np.array(mass_stride)
         data["mass"] = m.reshape(E, -1)[:, ::mass_stride].copy()
+        if full_mass_of is not None:
+            data["mass_full"] = m[full_mass_of].copy()  # one whole matrix next to the strided samples
+            data["mass_full_of"] = np.array(full_mass_of)
         data["mass_ref_domain"] = rd.mass(basis, basis, rules, 1).reshape(1, -1)[:, ::mass_stride].copy()
         data["primal"] = np.stack([np.linalg.solve(m[e], data["l2_dual"][e]) for e in range(E)])
     if extra:
@@ -78,8 +81,12 @@ def c5_gradient(data, geom, E):
 
 
 if __name__ == "__main__":
+    only = sys.argv[1:]
+    if only == ["c4"]:
+        make(syn.CONFIGS["c4"], 2, mass_stride=61, full_mass_of=1)
+        sys.exit(0)
     make(syn.CONFIGS["c1"], 16)
     make(syn.CONFIGS["c2"], 8)
     make(syn.CONFIGS["c3"], 3, with_mass=False, extra=c3_blocks)
-    make(syn.CONFIGS["c4"], 2, mass_stride=61)
+    make(syn.CONFIGS["c4"], 2, mass_stride=61, full_mass_of=1)
     make(syn.CONFIGS["c5"], 8, extra=c5_gradient)

@@ -31,6 +31,8 @@ def test_oracle_matches_golden(orc, name):
         s = int(g["mass_stride"])
         m = orc.mass(basis, basis, rules, E, det=det)
         assert np.array_equal(m.reshape(E, -1)[:, ::s], g["mass"])
+        if "mass_full" in g:
+            assert np.array_equal(m[int(g["mass_full_of"])], g["mass_full"])
         assert np.array_equal(m, np.swapaxes(m, 1, 2))  # exact mirror (mass_matrices.c:326-335)
         assert np.array_equal(orc.mass(basis, basis, rules, 1).reshape(1, -1)[:, ::s], g["mass_ref_domain"])
     if name == "c3":
