@@ -1562,6 +1562,30 @@ static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *b
     const std::string key_w = plan_key("mass", ndim, basis, basis, rules, nullptr, -1, 1, -1, 0);
     const std::string key_l2 = plan_key("l2g", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
     const std::string key_l2w = plan_key("l2", ndim, basis, nullptr, rules, nullptr, 1, 0, 0, 0);
+    if (ndim == 1 && n_phys == 1 && geom_basis[0].order == 1 && ctx->fastdiag && !ctx->force_generic)
+    {
+        // straight 1-D segments: the determinant is one number per element, M = det A, b = det Bw f, u = P f -- one launch
+        const std::string key_1d = plan_key("l2seg", ndim, basis, nullptr, rules, geom_basis, 2, 0, 0, 0);
+        const LaunchCfg probe_cfg = make_launch_cfg(ctx, ctx->stream);
+        const int probe = launch_l2_system_1d(ctx, probe_cfg, key_1d, basis[0], rules[0], geom_basis[0], 0, nullptr, nullptr, nullptr,
+                                              nullptr, nullptr);
+        if (probe == INTERP_SUCCESS)
+        {
+            std::vector<BatchArray> seg_arrays = {{ARR_IN, (void *)geom_dofs, sizeof(double) * 2},
+                                                  {ARR_IN, (void *)fvals, sizeof(double) * op.Q},
+                                                  {ARR_OUT, solve ? nullptr : mass, sizeof(double) * op.N_out * op.N_in},
+                                                  {ARR_OUT, rhs, sizeof(double) * op.N_in}};
+            return run_batched(ctx, n_elements, seg_arrays, where, 0, [&](const LaunchCfg &cfg, size_t, size_t cnt, void **dev) -> int {
+                if (!cnt)
+                    return INTERP_SUCCESS;
+                return launch_l2_system_1d(ctx, cfg, key_1d, basis[0], rules[0], geom_basis[0], cnt, (const double *)dev[0],
+                                           (const double *)dev[1], solve ? nullptr : (double *)dev[2], solve ? nullptr : (double *)dev[3],
+                                           solve ? (double *)dev[3] : nullptr);
+            });
+        }
+        if (probe != IB200_ERROR_UNSUPPORTED)
+            return probe;
+    }
     if (solve && fuse_geometry && ctx->fastdiag && !ctx->force_generic)
     {
         // bilinear quads: det J is linear in the reference coordinates, so M^-1 is two 1-D transforms and a diagonal

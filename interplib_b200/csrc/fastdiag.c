@@ -236,3 +236,77 @@ int ib200_tables_pair_moments(basis_spec_t bout, basis_spec_t bin, integration_s
     free(buf);
     return res;
 }
+
+/* P[i][q] = sum_j (A^-1)[i][j] w_q B_j(x_q): the L2 projector of the 1-D space on an element with CONSTANT Jacobian
+ * determinant (straight segments: M_e = det_e A, b_e = det_e Bw f_e, so u_e = P f_e whatever det_e is).  Long double
+ * Cholesky; INTERP_ERROR_BAD_SYSTEM when A is not positive definite. */
+int ib200_tables_projector_1d(basis_spec_t basis, integration_spec_t rule, double *P)
+{
+    const unsigned n = basis.order + 1, m = rule.order + 1;
+    double *B = (double *)malloc(sizeof(double) * (2 * (size_t)n * m + 2 * m));
+    real *work = (real *)malloc(sizeof(real) * (2 * (size_t)n * n + n));
+    if (!B || !work)
+    {
+        free(B);
+        free(work);
+        return INTERP_ERROR_FAILED_ALLOCATION;
+    }
+    double *D = B + (size_t)n * m, *x = D + (size_t)n * m, *w = x + m;
+    real *A = work, *L = A + n * n, *y = L + n * n;
+    int res = ib200_tables_rule(rule, x, w, NULL);
+    if (res == INTERP_SUCCESS)
+        res = ib200_tables_basis(basis, rule, B, D);
+    if (res != INTERP_SUCCESS)
+        goto done;
+    for (unsigned j = 0; j < n; ++j)
+        for (unsigned i = 0; i < n; ++i)
+        {
+            real a = 0.0L;
+            for (unsigned q = 0; q < m; ++q)
+                a += (real)w[q] * ((real)B[j * m + q] * (real)B[i * m + q]);
+            A[j * n + i] = a;
+        }
+    memset(L, 0, sizeof(real) * n * n);
+    for (unsigned j = 0; j < n; ++j)
+    {
+        real d = A[j * n + j];
+        for (unsigned k = 0; k < j; ++k)
+            d -= L[j * n + k] * L[j * n + k];
+        if (!(d > 1e-28L * fabsl(A[j * n + j])) || !(A[j * n + j] > 0.0L))
+        {
+            res = INTERP_ERROR_BAD_SYSTEM;
+            goto done;
+        }
+        L[j * n + j] = sqrtl(d);
+        for (unsigned i = j + 1; i < n; ++i)
+        {
+            real s = A[i * n + j];
+            for (unsigned k = 0; k < j; ++k)
+                s -= L[i * n + k] * L[j * n + k];
+            L[i * n + j] = s / L[j * n + j];
+        }
+    }
+    for (unsigned q = 0; q < m; ++q) /* column q of P solves A p = w_q B[:, q] */
+    {
+        for (unsigned i = 0; i < n; ++i)
+        {
+            real s = (real)w[q] * (real)B[i * m + q];
+            for (unsigned k = 0; k < i; ++k)
+                s -= L[i * n + k] * y[k];
+            y[i] = s / L[i * n + i];
+        }
+        for (unsigned ii = n; ii-- > 0;)
+        {
+            real s = y[ii];
+            for (unsigned k = ii + 1; k < n; ++k)
+                s -= L[k * n + ii] * y[k];
+            y[ii] = s / L[ii * n + ii];
+        }
+        for (unsigned i = 0; i < n; ++i)
+            P[i * m + q] = (double)y[i];
+    }
+done:
+    free(B);
+    free(work);
+    return res;
+}

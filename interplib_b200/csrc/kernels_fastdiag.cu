@@ -410,3 +410,127 @@ int launch_l2proj_fd2d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
 #undef IB_CASE
     return IB200_ERROR_UNSUPPORTED;
 }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// 1-D: straight segments (BASELINE config 1: mesh1d, p = 4, 8-point Gauss rule, mass matrix + L2 projection of sin(x)).
+// The Jacobian determinant of an order-1 coordinate map is one number per element, so everything the reference computes per
+// element (python/interplib/integration.py:106-223 over src/python/mass_matrices.c:264-335 and mappings.c:304-556) is a
+// table times that number:  M_e = det_e A,  b_e = det_e Bw f_e,  u_e = M_e^-1 b_e = P f_e  (P = A^-1 Bw, host, long double).
+// ONE launch instead of the three (system) or four (projection) generic ones: thread (e, j) writes row j of M_e and entry j
+// of b_e / u_e, consecutive threads write consecutive rows.  The configuration is launch-latency bound (1 024 elements).
+namespace
+{
+
+// tabs: A[n][n] | Bw[n][m] | P[n][m]
+__global__ void __launch_bounds__(256)
+    l2_system_1d_kernel(int n, int m, double s0, double s1, const double *__restrict__ tabs, size_t E, const double *__restrict__ geom,
+                        const double *__restrict__ f, double *__restrict__ M, double *__restrict__ b, double *__restrict__ u,
+                        int *__restrict__ status)
+{
+    const double *A = tabs, *Bw = tabs + n * n, *P = Bw + n * m;
+    const size_t total = E * (size_t)n;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x)
+    {
+        const size_t e = t / n;
+        const int j = (int)(t - e * n);
+        // dx/dxi = (0 + D0 c0) + D1 c1 with separate roundings, as compute_integration_point_values_derivatives does
+        const double det = __dadd_rn(__dmul_rn(s0, geom[2 * e]), __dmul_rn(s1, geom[2 * e + 1]));
+        if (M)
+        {
+            double *row = M + t * n;
+            for (int i = 0; i < n; ++i)
+                __stcs(row + i, __dmul_rn(det, A[j * n + i]));
+        }
+        if (b || u)
+        {
+            const double *fe = f + e * m;
+            double sb = 0.0, su = 0.0;
+            for (int q = 0; q < m; ++q)
+            {
+                const double fv = fe[q];
+                sb = fma(Bw[j * m + q], fv, sb);
+                su = fma(P[j * m + q], fv, su);
+            }
+            if (b)
+                b[t] = __dmul_rn(det, sb);
+            if (u)
+            {
+                u[t] = su;
+                if (!(fabs(det) > 0.0))
+                    atomicOr(status, IB200_STATUS_BAD_SYSTEM);
+            }
+        }
+    }
+}
+
+struct Seg1dPlan
+{
+    bool usable = false;
+    int n = 0, m = 0;
+    double s[2] = {0.0, 0.0};
+    double *d_tabs = nullptr;
+    ~Seg1dPlan()
+    {
+        if (d_tabs)
+            cudaFree(d_tabs);
+    }
+};
+
+} // namespace
+
+// geom[E][1][2] (DoFs of the order-1 geometry basis), fvals[E][m] -> any of mass[E][n][n], rhs[E][n], primal[E][n] (NULL: not
+// wanted).  IB200_ERROR_UNSUPPORTED (no error text) when the rule under-integrates the space; E == 0 with all outputs NULL
+// only answers whether the operation is inside the envelope.
+int launch_l2_system_1d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, basis_spec_t basis, integration_spec_t rule,
+                        basis_spec_t geom_basis, size_t E, const double *geom, const double *fvals, double *mass, double *rhs,
+                        double *primal)
+{
+    if (geom_basis.order != 1)
+        return IB200_ERROR_UNSUPPORTED;
+    auto it = ctx->plans.find(key);
+    if (it == ctx->plans.end())
+    {
+        auto plan = std::make_shared<Seg1dPlan>();
+        const int n = (int)basis.order + 1, m = (int)rule.order + 1;
+        plan->n = n;
+        plan->m = m;
+        std::vector<double> tabs((size_t)n * n + 2 * (size_t)n * m), X((size_t)n * n), B((size_t)n * m), D((size_t)n * m), x(m), w(m);
+        double a[2];
+        int res = ib200_tables_pair_moments(basis, basis, rule, tabs.data(), X.data());
+        if (res == INTERP_SUCCESS)
+            res = ib200_tables_rule(rule, x.data(), w.data(), nullptr);
+        if (res == INTERP_SUCCESS)
+            res = ib200_tables_basis(basis, rule, B.data(), D.data());
+        if (res == INTERP_SUCCESS)
+            res = ib200_tables_projector_1d(basis, rule, tabs.data() + (size_t)n * n + (size_t)n * m);
+        if (res == INTERP_SUCCESS)
+            res = ib200_tables_linear_basis(geom_basis, a, plan->s);
+        if (res == INTERP_SUCCESS)
+        {
+            for (int i = 0; i < n; ++i)
+                for (int q = 0; q < m; ++q)
+                    tabs[(size_t)n * n + (size_t)i * m + q] = B[(size_t)i * m + q] * w[q];
+            if (cudaMalloc((void **)&plan->d_tabs, tabs.size() * sizeof(double)) != cudaSuccess ||
+                cudaMemcpy(plan->d_tabs, tabs.data(), tabs.size() * sizeof(double), cudaMemcpyHostToDevice) != cudaSuccess)
+                return ib200_fail(IB200_ERROR_CUDA, "upload of the 1-D projection tables failed");
+            plan->usable = true;
+        }
+        else if (res != INTERP_ERROR_BAD_SYSTEM && res != IB200_ERROR_UNSUPPORTED)
+            return res;
+        it = ctx->plans.emplace(key, std::static_pointer_cast<void>(plan)).first;
+    }
+    const Seg1dPlan &plan = *static_cast<const Seg1dPlan *>(it->second.get());
+    if (!plan.usable)
+        return IB200_ERROR_UNSUPPORTED;
+    if (E == 0)
+        return INTERP_SUCCESS;
+    const size_t total = E * (size_t)plan.n;
+    const int grid = (int)std::max<size_t>(1, std::min<size_t>((total + 255) / 256, (size_t)cfg.sm_count * 8));
+    l2_system_1d_kernel<<<grid, 256, 0, cfg.stream>>>(plan.n, plan.m, plan.s[0], plan.s[1], plan.d_tabs, E, geom, fvals, mass, rhs, primal,
+                                                      cfg.status);
+    ++*cfg.launch_counter;
+    const cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess)
+        return ib200_fail(IB200_ERROR_CUDA, "launch of l2_system_1d_kernel failed: %s", cudaGetErrorString(err));
+    return INTERP_SUCCESS;
+}
