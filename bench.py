@@ -48,8 +48,8 @@ from interplib_b200 import synthetic as syn  # noqa: E402  (pure NumPy: does not
 NCU_TRAFFIC_BYTES = {
     "c2": (1970064432, 1 << 20),   # profiles/r01e_c2_eval2d_full.txt
     "c5": (5249943208, 1 << 20),   # profiles/r01c_c5_mass2d_lo_full.txt
-    "c4": None,
-    "c3": None,
+    "c4": (43730439000 + 20404992, 1 << 16),  # profiles/r02p_c4_mass2d_kron_staged_full.txt
+    "c3": (43427470000 + 17022720, 1 << 18),  # profiles/r02g_c3_mass2d_kron_full.txt
     "c1": None,
 }
 METRIC = {"c2": "basis_grad_evals_per_s"}
