@@ -523,23 +523,29 @@ class Runner:
         sub = -(-part.max_count // n_sub)
         d_norm = ctx.alloc(8 * n_sub)
 
+        n_gather = max(1, int(os.environ.get("IB200_BENCH_GATHER_PARTS", "1")))  # pieces the DoF gather is issued in
+
         def job(d_g, d_f, d_b, d_M, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub):
             """Mass matrices + L2 projection of `count` elements starting at global element `first` (this rank's block, or all
-            of them for the single-rank reference), pipelined in n_sub sub-slabs: primal DoFs first (fast diagonalisation),
-            their all-gather goes to the communicator's stream, the (M, b) assembly and the norm run meanwhile."""
+            of them for the single-rank reference): primal DoFs of the block first (fast diagonalisation), their all-gather
+            goes to the communicator's stream, the (M, b) assembly and the norms run meanwhile in n_sub sub-slabs."""
+            gsub = -(-part.max_count // n_gather)
+            for k in range(n_gather):
+                lo, hi = min(count, k * gsub), min(count, (k + 1) * gsub)
+                if hi > lo and compute:
+                    ctx.l2_project_mapped(basis, rules, gb, int(d_g) + lo * 64, cfg.n_phys, int(d_f) + lo * Q * 8,
+                                          out=int(d_all) + (first + lo) * N * 8, where=DEVICE, n_elements=hi - lo)
+                if collectives:
+                    counts, offsets = part.slab_layout(N, k * gsub, gsub)
+                    comm.allgatherv(int(d_all) + (part.first + min(part.count, k * gsub)) * N * 8, d_all, counts, offsets, overlap=True)
             for k in range(n_sub):
                 lo, hi = min(count, k * sub), min(count, (k + 1) * sub)
-                g, f = int(d_g) + lo * 64, int(d_f) + lo * Q * 8
-                u = int(d_all) + (first + lo) * N * 8
-                b = int(d_b) + lo * N * 8
-                M = int(d_M) + lo * N * N * 8
                 if hi > lo and compute:
-                    ctx.l2_project_mapped(basis, rules, gb, g, cfg.n_phys, f, out=u, where=DEVICE, n_elements=hi - lo)
-                if collectives:
-                    counts, offsets = part.slab_layout(N, k * sub, sub)
-                    comm.allgatherv(int(d_all) + (part.first + min(part.count, k * sub)) * N * 8, d_all, counts, offsets, overlap=True)
-                if hi > lo and compute:
-                    ctx.l2_system_mapped(basis, rules, gb, g, cfg.n_phys, f, mass=M, rhs=b, where=DEVICE, n_elements=hi - lo)
+                    g, f = int(d_g) + lo * 64, int(d_f) + lo * Q * 8
+                    u = int(d_all) + (first + lo) * N * 8
+                    b = int(d_b) + lo * N * 8
+                    ctx.l2_system_mapped(basis, rules, gb, g, cfg.n_phys, f, mass=int(d_M) + lo * N * N * 8, rhs=b, where=DEVICE,
+                                         n_elements=hi - lo)
                     ctx.dot(b, u, out=int(d_norm) + 8 * k, where=DEVICE, n=(hi - lo) * N)
             if collectives:
                 comm.allreduce_sums(int(d_norm), n_sub)
@@ -626,8 +632,8 @@ class Runner:
                                "diagonalisation), element mass matrices M + right-hand sides b (ib200_l2_system_mapped_batch; M stays "
                                "resident and sharded, 5 000 B per element), norm b.u (ib200_dot); then NCCL all-gather of the [E,25] primal "
                                "DoFs to every rank and all-reduce of the norms, issued through the C ABI, all inside the CUDA-event region",
-                       "pipeline": f"{n_sub} sub-slabs per rank; the all-gather of a sub-slab's DoFs runs on the communicator's "
-                                   "(high-priority) stream while its mass matrices and the next sub-slab are computed",
+                       "pipeline": f"primal DoFs of the rank's block first; their all-gather ({n_gather} part(s)) runs on the communicator's "
+                                   f"(high-priority) stream while the mass matrices and right-hand sides are assembled in {n_sub} sub-slabs",
                        "parallelism": f"element block partition x{world}, NCCL {nccl} all-gather + all-reduce",
                        "gather_path": ("copy-engine pushes into IPC-mapped peer buffers over NVLink (ib200_comm_register_gather), arrival "
                                        "published by a one-double NCCL all-reduce") if p2p else "NCCL broadcasts grouped per sub-slab"},
