@@ -1,7 +1,7 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-for mode in p2p; do
+for mode in p2p nccl; do
   if [ $mode = nccl ]; then export IB200_NO_P2P_GATHER=1; fi
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --no-cpu-baseline --no-e2e --no-mass > gpurun_out/r02m_bench_n8_$mode.json 2> gpurun_out/r02m_bench_n8_$mode.err; echo "bench8 $mode rc=$?"; tail -c 400 gpurun_out/r02m_bench_n8_$mode.err | grep -v "OMP\|\*\*\*"
   python - <<PY
