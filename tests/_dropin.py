@@ -36,6 +36,8 @@ def make_layout(kind: str, tmp: Path) -> Path:
     """Directory to put first on PYTHONPATH."""
     if kind == "package":
         return ROOT / "dropin"
+    if kind == "reference":  # the compiled reference itself (oracle/_ref): the oracle's self-test, nothing of this repo
+        return ROOT / "oracle" / "_ref"
     assert kind == "extension"
     pkg = tmp / "ext_layout" / "interplib"
     pkg.mkdir(parents=True, exist_ok=True)
