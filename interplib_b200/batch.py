@@ -52,7 +52,7 @@ def _ptr(a):
         return None
     if isinstance(a, np.ndarray):
         return a.ctypes.data_as(C.c_void_p)
-    return C.c_void_p(int(a))  # raw device / pinned address
+    return C.c_void_p(int(a))  # raw device / pinned address, DeviceBuffer, DeviceArray
 
 
 class DeviceBuffer:
@@ -84,6 +84,53 @@ class DeviceBuffer:
 
     def __int__(self) -> int:
         return int(self.ptr)
+
+
+class DeviceArray:
+    """A float64 array that lives in device memory: what the batched calls return when their inputs are device arrays, so
+    that chains (geometry + f -> primal DoFs -> values and gradients at the rule nodes -> ...) never cross PCIe.  Explicit
+    transfers only: :meth:`Context.to_device`, :meth:`to_host`.  ``int(a)`` is the device address (usable wherever the
+    ``where=DEVICE`` form of a call takes a raw pointer)."""
+
+    def __init__(self, ctx: "Context", shape, buf: DeviceBuffer | None = None):
+        self.ctx = ctx
+        self.shape = tuple(int(v) for v in shape)
+        self.size = int(np.prod(self.shape, dtype=np.int64))
+        self.buf = buf if buf is not None else DeviceBuffer(ctx, max(self.size, 1) * 8)
+        assert self.buf.nbytes >= self.size * 8
+
+    @property
+    def ptr(self) -> int:
+        return self.buf.ptr
+
+    def __int__(self) -> int:
+        return int(self.buf.ptr)
+
+    def reshape(self, *shape) -> "DeviceArray":
+        """A view of the same memory with another shape (one ``-1`` allowed)."""
+        shape = tuple(shape[0]) if len(shape) == 1 and isinstance(shape[0], (tuple, list)) else tuple(shape)
+        known = int(np.prod([v for v in shape if v != -1], dtype=np.int64))
+        shape = tuple(self.size // max(known, 1) if v == -1 else int(v) for v in shape)
+        if int(np.prod(shape, dtype=np.int64)) != self.size:
+            raise ValueError(f"cannot reshape a device array of {self.size} values to {shape}")
+        return DeviceArray(self.ctx, shape, self.buf)
+
+    def to_host(self) -> np.ndarray:
+        self.ctx.synchronize()
+        return self.buf.download(self.shape)
+
+    def free(self) -> None:
+        self.buf.free()
+
+
+def _is_dev(*arrays) -> bool:
+    return any(isinstance(a, DeviceArray) for a in arrays)
+
+
+def _dev_in(a, shape, name="input") -> "DeviceArray":
+    if not isinstance(a, DeviceArray):
+        raise TypeError(f"{name}: device-resident calls take DeviceArray inputs throughout (Context.to_device), got {type(a).__name__}")
+    return a.reshape(shape)
 
 
 class PinnedArray:
@@ -168,6 +215,21 @@ class Context:
     def pinned(self, shape, dtype=np.float64) -> PinnedArray:
         return PinnedArray(self, shape, dtype)
 
+    def to_device(self, host) -> DeviceArray:
+        """Copy a NumPy array to the device; the batched calls keep their results there when given such inputs."""
+        host = np.ascontiguousarray(host, dtype=np.float64)
+        d = DeviceArray(self, host.shape)
+        if host.size:
+            d.buf.upload(host)
+        return d
+
+    def _dev_out(self, out, shape) -> DeviceArray:
+        if out is None:
+            return DeviceArray(self, shape)
+        if not isinstance(out, DeviceArray) or out.size != int(np.prod(shape, dtype=np.int64)):
+            raise ValueError(f"out must be a DeviceArray of {int(np.prod(shape, dtype=np.int64))} values")
+        return out.reshape(shape)
+
     def timer_start(self, slot: int = 0) -> None:
         check(lib.ib200_timer_start(self.handle, slot))
 
@@ -184,6 +246,10 @@ class Context:
         """dofs[E][N] -> out[E][n_fields][Q]   (ib200_reconstruct_batch)"""
         N, Q = _n_basis(basis), _n_points(rules)
         masks = (C.c_uint * len(deriv_masks))(*[int(m) for m in deriv_masks])
+        if _is_dev(dofs, out):
+            dofs = _dev_in(dofs, (-1, N), "dofs")
+            where, n_elements = DEVICE, dofs.shape[0]
+            out = self._dev_out(out, (n_elements, len(deriv_masks), Q))
         if where == HOST:
             dofs = _as_in(dofs, (-1, N))
             E = dofs.shape[0]
@@ -230,6 +296,10 @@ class Context:
         """dofs[E][N] -> DoFs of d/dxi_idim in the space one order lower along idim   (ib200_dof_derivative_batch)"""
         N = _n_basis(basis)
         lower = [(t, o - 1 if k == idim else o) for k, (t, o) in enumerate(basis)]
+        if _is_dev(dofs, out):
+            dofs = _dev_in(dofs, (-1, N), "dofs")
+            where, n_elements = DEVICE, dofs.shape[0]
+            out = self._dev_out(out, (n_elements, _n_basis(lower) if 0 <= idim < len(basis) and basis[idim][1] > 0 else 0))
         if where == HOST:
             dofs = _as_in(dofs, (-1, N))
             E = dofs.shape[0]
@@ -245,6 +315,12 @@ class Context:
                  coords=None, det=None, jinv=None):
         """geom_dofs[E][n_phys][Ng] -> coords[E][n_phys][1+d][Q], det[E][Q], jinv[E][Q][d][n_phys]"""
         Ng, Q, d = _n_basis(geom_basis), _n_points(rules), len(geom_basis)
+        if _is_dev(geom_dofs, coords, det, jinv):
+            geom_dofs = _dev_in(geom_dofs, (-1, n_phys, Ng), "geom_dofs")
+            where, n_elements = DEVICE, geom_dofs.shape[0]
+            coords = self._dev_out(coords, (n_elements, n_phys, 1 + d, Q)) if "coords" in want else None
+            det = self._dev_out(det, (n_elements, Q)) if "det" in want else None
+            jinv = self._dev_out(jinv, (n_elements, Q, d, n_phys)) if "jinv" in want else None
         if where == HOST:
             geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
             E = geom_dofs.shape[0]
@@ -274,6 +350,10 @@ class Context:
                            where=HOST, n_elements=None):
         """geometry fused: geom_dofs[E][n_phys][Ng] -> out[E][N_out][N_in]   (ib200_mass_matrix_mapped_batch)"""
         Nin, Nout, Ng = _n_basis(basis_in), _n_basis(basis_out), _n_basis(geom_basis)
+        if _is_dev(geom_dofs, out):
+            geom_dofs = _dev_in(geom_dofs, (-1, n_phys, Ng), "geom_dofs")
+            where, n_elements = DEVICE, geom_dofs.shape[0]
+            out = self._dev_out(out, (n_elements, Nout, Nin))
         if where == HOST:
             geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
             E = geom_dofs.shape[0]
@@ -304,6 +384,11 @@ class Context:
     def l2_dual_mapped(self, basis, rules, geom_basis, geom_dofs, n_phys, fvals, out=None, where=HOST, n_elements=None):
         """geometry fused   (ib200_l2_dual_mapped_batch)"""
         N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if _is_dev(geom_dofs, fvals, out):
+            fvals = _dev_in(fvals, (-1, Q), "fvals")
+            where, n_elements = DEVICE, fvals.shape[0]
+            geom_dofs = _dev_in(geom_dofs, (n_elements, n_phys, Ng), "geom_dofs")
+            out = self._dev_out(out, (n_elements, N))
         if where == HOST:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
@@ -319,6 +404,12 @@ class Context:
                          n_elements=None):
         """K2 + K3 in one pass: (mass[E][N][N], rhs[E][N]) of the L2 projection   (ib200_l2_system_mapped_batch)"""
         N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if _is_dev(geom_dofs, fvals, mass, rhs):
+            fvals = _dev_in(fvals, (-1, Q), "fvals")
+            where, n_elements = DEVICE, fvals.shape[0]
+            geom_dofs = _dev_in(geom_dofs, (n_elements, n_phys, Ng), "geom_dofs")
+            mass = self._dev_out(mass, (n_elements, N, N))
+            rhs = self._dev_out(rhs, (n_elements, N))
         if where == HOST:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
@@ -337,6 +428,10 @@ class Context:
         """The whole k-form element mass matrix M[E][N][N] (N = n_dofs = kform_dof_count): block (a, b) over the component
         spaces = compute_mass_matrix(space_b, space_a, smap); one launch for bilinear quads   (ib200_kform_mass_mapped_batch)"""
         Ng = _n_basis(geom_basis)
+        if _is_dev(geom_dofs, out):
+            geom_dofs = _dev_in(geom_dofs, (-1, n_phys, Ng), "geom_dofs")
+            where, n_elements = DEVICE, geom_dofs.shape[0]
+            out = self._dev_out(out, (n_elements, n_dofs, n_dofs))
         if where == HOST:
             geom_dofs = _as_in(geom_dofs, (-1, n_phys, Ng))
             E = geom_dofs.shape[0]
@@ -352,6 +447,11 @@ class Context:
         """projection_l2_primal of a whole batch: geometry + f samples -> primal DoFs u[E][N]; the mass matrices stay in
         device scratch   (ib200_l2_project_mapped_batch)"""
         N, Q, Ng = _n_basis(basis), _n_points(rules), _n_basis(geom_basis)
+        if _is_dev(geom_dofs, fvals, out):
+            fvals = _dev_in(fvals, (-1, Q), "fvals")
+            where, n_elements = DEVICE, fvals.shape[0]
+            geom_dofs = _dev_in(geom_dofs, (n_elements, n_phys, Ng), "geom_dofs")
+            out = self._dev_out(out, (n_elements, N))
         if where == HOST:
             fvals = _as_in(fvals, (-1, Q))
             E = fvals.shape[0]
@@ -364,7 +464,12 @@ class Context:
         return out
 
     def spd_solve(self, mass, rhs, where=HOST, n=None, n_elements=None):
-        """Solve mass[e] u = rhs[e] for every element (Cholesky on the GPU); returns u[E][N]."""
+        """Solve mass[e] u = rhs[e] for every element (Cholesky on the GPU); returns u[E][N].  Device arrays are solved in
+        place: ``rhs`` is overwritten with u (and returned), ``mass`` with its factor."""
+        if _is_dev(mass, rhs):
+            if not (isinstance(mass, DeviceArray) and isinstance(rhs, DeviceArray)):
+                raise TypeError("spd_solve: mass and rhs must both be device arrays")
+            where, n_elements, n = DEVICE, rhs.shape[0], rhs.size // max(rhs.shape[0], 1)
         if where == HOST:
             rhs = np.array(rhs, dtype=np.float64, order="C", copy=True)
             E, n = rhs.shape
@@ -378,7 +483,12 @@ class Context:
     # -- norms ---------------------------------------------------------------------------------------
     def dot(self, a, b, out=None, where=HOST, n=None):
         """sum_i a[i]*b[i] with a fixed reduction tree (ib200_dot).  Host arrays -> float; device pointers -> the
-        result is left in ``out`` (device pointer to one double)."""
+        result is left in ``out`` (device pointer to one double); device arrays -> a one-element device array."""
+        if _is_dev(a, b, out):
+            if not (isinstance(a, DeviceArray) and isinstance(b, DeviceArray)) or a.size != b.size:
+                raise ValueError("dot: operands must be device arrays of the same size")
+            where, n = DEVICE, a.size
+            out = self._dev_out(out, (1,))
         if where == HOST:
             a = np.ascontiguousarray(a, dtype=np.float64).reshape(-1)
             b = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)

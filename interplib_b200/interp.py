@@ -23,7 +23,8 @@ from ._lib import BASIS_TYPES, RULE_TYPES
 __all__ = [
     "BasisType", "IntegrationMethod", "IntegrationRegistry", "IntegrationSpecs", "IntegrationSpace", "BasisRegistry",
     "BasisSpecs", "FunctionSpace", "DegreesOfFreedom", "CoordinateMap", "SpaceMap", "compute_mass_matrix",
-    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct", "reconstruct_batch", "incidence_matrix",
+    "compute_gradient_mass_matrix", "projection_l2_dual", "projection_l2_primal", "integrate_callable", "reconstruct", "reconstruct_batch", "DegreesOfFreedomBatch",
+    "projection_l2_primal_batch", "incidence_matrix",
     "compute_dual_degrees_of_freedom", "DEFAULT_INTEGRATION_REGISTRY", "DEFAULT_BASIS_REGISTRY",
 ]
 
@@ -638,6 +639,82 @@ def reconstruct(dof: DegreesOfFreedom, *x) -> np.ndarray:
             raise ValueError("All input coordinate arrays must have the same shape.")
     phi = dof.function_space.evaluate(*xs).reshape((-1, dof.n_dofs))
     return np.sum(phi * dof.values.flatten(), axis=-1).reshape(xs[0].shape)
+
+
+class DegreesOfFreedomBatch:
+    """E stacked :class:`DegreesOfFreedom` of one function space, resident on the host (NumPy ``[E, n0, n1, ..]``) or on the
+    device (``batch.DeviceArray``).  The element-batched counterpart of the reference's per-element object: its methods are
+    one GPU launch for all E elements, and on a device-resident batch inputs and results stay in HBM -- chains such as
+    ``projection_l2_primal_batch(...).reconstruct_at_integration_points(...)`` never cross PCIe until ``to_host()``."""
+
+    def __init__(self, function_space: FunctionSpace, values):
+        if not isinstance(function_space, FunctionSpace):
+            raise TypeError(f"Expected FunctionSpace, got {type(function_space).__name__}")
+        self._fs = function_space
+        if isinstance(values, batch.DeviceArray):
+            self._values = values.reshape((-1,) + function_space.shape)
+        else:
+            arr = np.ascontiguousarray(values, dtype=np.float64)
+            if arr.size % function_space.n_basis:
+                raise ValueError(f"values must hold a multiple of {function_space.n_basis} entries")
+            self._values = arr.reshape((-1,) + function_space.shape)
+
+    function_space = property(lambda self: self._fs)
+    n_elements = property(lambda self: self._values.shape[0])
+    on_device = property(lambda self: isinstance(self._values, batch.DeviceArray))
+    values = property(lambda self: self._values)
+
+    def to_device(self) -> "DegreesOfFreedomBatch":
+        return self if self.on_device else DegreesOfFreedomBatch(self._fs, _ctx().to_device(self._values))
+
+    def to_host(self) -> "DegreesOfFreedomBatch":
+        return DegreesOfFreedomBatch(self._fs, self._values.to_host()) if self.on_device else self
+
+    def __getitem__(self, e: int) -> DegreesOfFreedom:
+        """Element e as the reference's per-element object (host batches)."""
+        if self.on_device:
+            raise TypeError("index a host batch (to_host() first)")
+        return DegreesOfFreedom(self._fs, self._values[e])
+
+    def reconstruct_at_integration_points(self, integration_space: IntegrationSpace, idim: Sequence[Sequence[int]] = ((),)):
+        """``[E, n_fields, m0, m1, ..]``: field k is the reconstruction differentiated once along every dimension listed in
+        ``idim[k]`` (``()`` = the values) -- DegreesOfFreedom.reconstruct[_derivative]_at_integration_points for all
+        elements in one launch (src/python/degrees_of_freedom.c:426-722)."""
+        masks = []
+        for dims in idim:
+            m = 0
+            for k in dims:
+                if not 0 <= int(k) < self._fs.dimension or (m >> int(k)) & 1:
+                    raise ValueError(f"Invalid or repeated derivative dimension {k}.")
+                m |= 1 << int(k)
+            masks.append(m)
+        flat = self._values.reshape(self.n_elements, -1)
+        out = _ctx().reconstruct(self._fs.basis, integration_space.rules, flat, masks)
+        return out.reshape((self.n_elements, len(masks)) + tuple(o + 1 for o in integration_space.orders))
+
+    def derivative(self, idim: int) -> "DegreesOfFreedomBatch":
+        """DegreesOfFreedom.derivative for every element (src/python/degrees_of_freedom.c:853-945), bit-identical."""
+        out = _ctx().dof_derivative(self._fs.basis, self._values.reshape(self.n_elements, -1), int(idim))
+        return DegreesOfFreedomBatch(self._fs.lower_order(int(idim)), out)
+
+
+def projection_l2_primal_batch(fvals, function_space: FunctionSpace, integration_space: IntegrationSpace, geom_dofs,
+                               geom_space: FunctionSpace, n_phys: int | None = None) -> DegreesOfFreedomBatch:
+    """projection_l2_primal (python/interplib/integration.py:171-223) for E elements at once: ``fvals[E, m0, m1, ..]`` are the
+    samples of f at the mapped rule nodes, ``geom_dofs[E, n_phys, ...]`` the coordinate DoFs of ``geom_space`` (for
+    ``Quad.from_corners`` elements: order-1 ``lagrange-uniform``).  NumPy inputs give a host batch, ``DeviceArray`` inputs a
+    device-resident one (ib200_l2_project_mapped_batch: fast diagonalisation on bilinear quads, no mass matrix)."""
+    n_phys = function_space.dimension if n_phys is None else int(n_phys)
+    Q = int(np.prod([o + 1 for o in integration_space.orders]))
+    dev = isinstance(fvals, batch.DeviceArray) or isinstance(geom_dofs, batch.DeviceArray)
+    if dev:
+        f2 = fvals.reshape(-1, Q)
+        g2 = geom_dofs.reshape(f2.shape[0], n_phys, geom_space.n_basis)
+    else:
+        f2 = np.ascontiguousarray(fvals, dtype=np.float64).reshape(-1, Q)
+        g2 = np.ascontiguousarray(geom_dofs, dtype=np.float64).reshape(f2.shape[0], n_phys, geom_space.n_basis)
+    u = _ctx().l2_project_mapped(function_space.basis, integration_space.rules, geom_space.basis, g2, n_phys, f2)
+    return DegreesOfFreedomBatch(function_space, u)
 
 
 def reconstruct_batch(function_space: FunctionSpace, dof_values, *x, idim: Sequence[int] = ()) -> np.ndarray:

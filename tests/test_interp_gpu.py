@@ -242,3 +242,40 @@ def test_reconstruct_batch_matches_per_element_reconstruct():
         reconstruct_batch(fs, vals, x, y, idim=[0, 0])
     with pytest.raises(TypeError):
         reconstruct_batch(fs, vals, x)
+
+
+def test_device_resident_chain_equals_host_path(ctx):
+    """a chain through the drop-in layer that never crosses PCIe -- corner coordinates + samples of f on the
+    device -> primal DoFs (projection_l2_primal_batch) -> their derivative DoFs -> values and gradients at the rule nodes ->
+    to_host() -- gives, bit for bit, what the same calls give on NumPy arrays; and element e of the batch is what the
+    reference-style per-element objects compute."""
+    import interplib_b200.interp as ip
+    from interplib_b200 import batch, synthetic as syn
+
+    rng = np.random.default_rng(91)
+    E = 515
+    fs = ip.FunctionSpace(ip.BasisSpecs("lagrange-gauss-lobatto", 4), ip.BasisSpecs("lagrange-gauss-lobatto", 4))
+    gs = ip.FunctionSpace(ip.BasisSpecs("lagrange-uniform", 1), ip.BasisSpecs("lagrange-uniform", 1))
+    isp = ip.IntegrationSpace(ip.IntegrationSpecs(5), ip.IntegrationSpecs(5))
+    geom = syn.quad_mesh_geometry(1024, seed=2).reshape(1024, 2, 2, 2)[:E].copy()
+    f = rng.standard_normal((E, 6, 6))
+    host = ip.projection_l2_primal_batch(f, fs, isp, geom, gs)
+    assert not host.on_device and host.values.shape == (E, 5, 5)
+    c = ip._ctx()
+    dev = ip.projection_l2_primal_batch(c.to_device(f), fs, isp, c.to_device(geom), gs)
+    assert dev.on_device and isinstance(dev.values, batch.DeviceArray)
+    fields = ((), (0,), (1,))
+    rec_d = dev.reconstruct_at_integration_points(isp, fields)
+    der_d = dev.derivative(1)
+    assert isinstance(rec_d, batch.DeviceArray) and der_d.on_device and der_d.function_space.orders == (4, 3)
+    assert np.array_equal(dev.to_host().values, host.values)
+    assert np.array_equal(rec_d.to_host(), host.reconstruct_at_integration_points(isp, fields))
+    assert np.array_equal(der_d.to_host().values, host.derivative(1).values)
+    # element 7 through the per-element objects of the reference's API
+    one = host[7]
+    rec = rec_d.to_host()
+    assert np.abs(one.reconstruct_at_integration_points(isp) - rec[7, 0]).max() <= 1e-13 * np.abs(rec[7, 0]).max()
+    assert np.abs(one.reconstruct_derivative_at_integration_points(isp, [1]) - rec[7, 2]).max() <= 1e-13 * np.abs(rec[7, 2]).max()
+    assert np.array_equal(one.derivative(1).values, der_d.to_host().values[7])
+    for a in (rec_d, der_d.values, dev.values):
+        a.free()
