@@ -210,6 +210,8 @@ extern "C" int ib200_comm_destroy(ib200_comm_t *comm)
     if (comm->ctx)
         cudaSetDevice(comm->ctx->device);
     ib200_comm_unregister_gather(comm);
+    if (comm->flag)
+        cudaFree(comm->flag);
     if (comm->side)
     {
         cudaStreamSynchronize(comm->side);
