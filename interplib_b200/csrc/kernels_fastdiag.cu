@@ -80,6 +80,18 @@ struct FdTabs
     double G[3][4];   // (x_xi0, x_xi1, x_xi0xi1) = G (c00, c01, c10, c11): coefficients of the bilinear coordinate map
 };
 
+// 1 / d to an ulp or two: hardware seed (about 20 bits) and two Newton steps.  __drcp_rn costs about twice the FP64
+// instructions for its exact rounding and special cases; d is a Jacobian determinant here, far from the subnormal range.
+__device__ __forceinline__ double fd_rcp(double d)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    double e = fma(-d, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-d, r, 1.0);
+    return fma(r, e, r);
+}
+
 // difference of products a*b - c*d with the rounding error of the second product recovered (Kahan)
 __device__ __forceinline__ double fd_diff_of_products(double a, double b, double c, double d)
 {
@@ -98,6 +110,12 @@ __global__ void __launch_bounds__(kFdWarps * 32)
     constexpr int EPB = EPW * kFdWarps;
     constexpr int Q = M * M;
     constexpr int NP = N + (N & 1); // even row pitch of the stage-3 tile: 16-byte aligned rows
+    // element pitch of the f tile: with an even Q the rows are read as 16-byte words, and a pitch whose half is odd puts the
+    // words of the warp's elements into different bank groups (Q = 36: 288 B apart, elements 0/4 and 1/5 collided; ncu:
+    // L1/shared pipe 82 % busy) -- the tile then arrives as one bulk copy per element instead of one per tile
+    // (measured dead end: one 288-byte bulk copy per element instead of one per tile made C5 27 % slower)
+    constexpr int QP = Q;
+    constexpr bool PER_ELEMENT = false;
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -108,10 +126,10 @@ __global__ void __launch_bounds__(kFdWarps * 32)
 
     // dynamic shared memory: f tiles | corner tiles | stage-3 tiles (per warp) | mbarriers
     extern __shared__ __align__(128) double dyn_smem[];
-    auto ftile = [&](int b) -> double * { return dyn_smem + b * (EPB * Q); };
-    auto gtile = [&](int b) -> double * { return dyn_smem + 2 * EPB * Q + b * (EPB * 8); };
-    double *tsm = dyn_smem + 2 * EPB * Q + 2 * EPB * 8 + (size_t)(warp * EPW + (active ? el : 0)) * (N * NP);
-    unsigned long long *bar = reinterpret_cast<unsigned long long *>(dyn_smem + 2 * EPB * Q + 2 * EPB * 8 + (size_t)EPB * N * NP);
+    auto ftile = [&](int b) -> double * { return dyn_smem + b * (EPB * QP); };
+    auto gtile = [&](int b) -> double * { return dyn_smem + 2 * EPB * QP + b * (EPB * 8); };
+    double *tsm = dyn_smem + 2 * EPB * QP + 2 * EPB * 8 + (size_t)(warp * EPW + (active ? el : 0)) * (N * NP);
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(dyn_smem + 2 * EPB * QP + 2 * EPB * 8 + (size_t)EPB * N * NP);
 
     // lane-private tables of dimension 1: Vw1[i1][:], xi1[:] * Vw1[i1][:], V1[i1][:], lambda1[i1]
     // dim1 layout: Vw1[N][M] | V1[N][N] | lam1[N] | xi1[M]
@@ -149,7 +167,13 @@ __global__ void __launch_bounds__(kFdWarps * 32)
         const int n = tile_elems(t);
         const unsigned fb = n * Q * sizeof(double), gb = n * 8 * sizeof(double);
         fd_mbar_expect_tx(&bar[b], fb + gb);
-        fd_bulk_g2s(ftile(b), fvals + t * (size_t)EPB * Q, fb, &bar[b]);
+        if (PER_ELEMENT)
+        {
+            for (int k = 0; k < n; ++k)
+                fd_bulk_g2s(ftile(b) + k * QP, fvals + (t * (size_t)EPB + k) * Q, Q * sizeof(double), &bar[b]);
+        }
+        else
+            fd_bulk_g2s(ftile(b), fvals + t * (size_t)EPB * Q, fb, &bar[b]);
         fd_bulk_g2s(gtile(b), geom + t * (size_t)EPB * 8, gb, &bar[b]);
     };
 
@@ -187,7 +211,7 @@ __global__ void __launch_bounds__(kFdWarps * 32)
         {
             const double *src = fvals + t * (size_t)EPB * Q;
             for (int idx = threadIdx.x; idx < n_here * Q; idx += blockDim.x)
-                ftile(cur)[idx] = src[idx];
+                ftile(cur)[(idx / Q) * QP + idx % Q] = src[idx];
             const double *gsrc = geom + t * (size_t)EPB * 8;
             for (int idx = threadIdx.x; idx < n_here * 8; idx += blockDim.x)
                 gtile(cur)[idx] = gsrc[idx];
@@ -199,7 +223,17 @@ __global__ void __launch_bounds__(kFdWarps * 32)
         if (work)
         {
             // det J = alpha + beta xi0 + gamma xi1 from the corner coordinates [c][i0][i1]
-            const double *gc = gtile(cur) + slot * 8;
+            double gc[8]; // four 16-byte loads (the corner block of an element is 64-byte aligned)
+            {
+                const double2 *g2 = reinterpret_cast<const double2 *>(gtile(cur) + slot * 8);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                {
+                    const double2 v = g2[k];
+                    gc[2 * k] = v.x;
+                    gc[2 * k + 1] = v.y;
+                }
+            }
             double dx[3], dy[3];
 #pragma unroll
             for (int k = 0; k < 3; ++k)
@@ -219,7 +253,7 @@ __global__ void __launch_bounds__(kFdWarps * 32)
             const double gamma = fd_diff_of_products(dx[2], dy[1], dx[1], dy[2]);
 
             // stages 1 and 2
-            const double *f = ftile(cur) + slot * Q;
+            const double *f = ftile(cur) + slot * QP;
             double sv[M];
 #pragma unroll
             for (int q0 = 0; q0 < M; ++q0)
@@ -245,7 +279,7 @@ __global__ void __launch_bounds__(kFdWarps * 32)
                     b = fma(tab.Vw0[i0][q0], sv[q0], b);
                 const double d = fma(beta, tab.lam0[i0], d1);
                 bad = bad || !(fabs(d) > 0.0);
-                ut[i0] = __dmul_rn(b, __drcp_rn(d));
+                ut[i0] = __dmul_rn(b, fd_rcp(d));
             }
             // stage 3
 #pragma unroll
@@ -315,7 +349,8 @@ int launch_fd_one(const LaunchCfg &cfg, const FdPlan &plan, size_t E, const doub
     std::memcpy(tab.G, plan.G, sizeof tab.G);
     constexpr int EPW = 32 / N, EPB = EPW * kFdWarps, NP = N + (N & 1);
     const size_t n_tiles = (E + EPB - 1) / EPB;
-    const size_t smem_bytes = sizeof(double) * (2 * EPB * M * M + 2 * EPB * 8 + EPB * N * NP) + 16;
+    constexpr int Q = M * M, QP = Q;
+    const size_t smem_bytes = sizeof(double) * (2 * EPB * QP + 2 * EPB * 8 + EPB * N * NP) + 16;
     if (smem_bytes > 200 * 1024)
         return IB200_ERROR_UNSUPPORTED;
     auto kernel = l2proj_fd2d_kernel<N, M>;
