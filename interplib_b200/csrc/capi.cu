@@ -1315,6 +1315,13 @@ static int mapped_mass_launch(ib200_ctx *ctx, const LaunchCfg &cfg, const Mapped
 {
     if (!cnt)
         return INTERP_SUCCESS;
+    if (!cfg.force_generic && ctx->kron && m.ndim == 3 && m.n_phys == 3 && m.deriv < 0)
+    {
+        // trilinear hexahedra: det J is a 27-term polynomial, the mass matrix a 27-term Kronecker sum (kernels_mass3d_kron.cu)
+        const int res = launch_mass3d_kron(ctx, cfg, m.key_kron, m.basis_out, m.basis_in, m.rules, m.geom_basis, cnt, geom, out);
+        if (res != IB200_ERROR_UNSUPPORTED)
+            return res;
+    }
     if (!cfg.force_generic && m.fuse_geometry)
     {
         int res = launch_mass2d_bilinear(ctx, cfg, m, cnt, geom, out);

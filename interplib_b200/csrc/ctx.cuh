@@ -209,6 +209,8 @@ int launch_mass2d_lo(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &ke
                      const double *wsrc, double *out, const double *fvals = nullptr, double *rhs = nullptr);
 int launch_l2dual2d_fast(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const OpDesc &op, const OpHost &host,
                          int wsrc, const OpHost *geom_host, size_t E, const double *fvals, const double *aux, double *out);
+int launch_mass3d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const basis_spec_t *rows, const basis_spec_t *cols,
+                       const integration_spec_t *rules, const basis_spec_t *geom_basis, size_t E, const double *geom, double *out);
 int launch_l2_system_1d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, basis_spec_t basis, integration_spec_t rule,
                         basis_spec_t geom_basis, size_t E, const double *geom, const double *fvals, double *mass, double *rhs,
                         double *primal);

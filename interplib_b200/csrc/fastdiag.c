@@ -310,3 +310,38 @@ done:
     free(work);
     return res;
 }
+
+/* Moments 0..kmax of the products of two 1-D bases: out[k][j][i] = sum_q w_q x_q^k Bout_j(x_q) Bin_i(x_q), long double.
+ * The Jacobian determinant of a trilinear hexahedron is a polynomial of degree 2 in each reference coordinate, so its mass
+ * matrix is a 27-term Kronecker sum of these tables (kernels_mass3d_kron.cu). */
+int ib200_tables_pair_moments_k(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, unsigned kmax, double *out)
+{
+    const unsigned no = bout.order + 1, ni = bin.order + 1, m = rule.order + 1;
+    double *buf = (double *)malloc(sizeof(double) * (2 * (size_t)(no + ni) * m + 2 * m));
+    if (!buf)
+        return INTERP_ERROR_FAILED_ALLOCATION;
+    double *Bo = buf, *Do = Bo + (size_t)no * m, *Bi = Do + (size_t)no * m, *Di = Bi + (size_t)ni * m, *x = Di + (size_t)ni * m,
+           *w = x + m;
+    int res = ib200_tables_rule(rule, x, w, NULL);
+    if (res == INTERP_SUCCESS)
+        res = ib200_tables_basis(bout, rule, Bo, Do);
+    if (res == INTERP_SUCCESS)
+        res = ib200_tables_basis(bin, rule, Bi, Di);
+    if (res == INTERP_SUCCESS)
+        for (unsigned j = 0; j < no; ++j)
+            for (unsigned i = 0; i < ni; ++i)
+                for (unsigned k = 0; k <= kmax; ++k)
+                {
+                    real acc = 0.0L;
+                    for (unsigned q = 0; q < m; ++q)
+                    {
+                        real p = (real)w[q] * ((real)Bo[j * m + q] * (real)Bi[i * m + q]);
+                        for (unsigned r = 0; r < k; ++r)
+                            p *= (real)x[q];
+                        acc += p;
+                    }
+                    out[((size_t)k * no + j) * ni + i] = (double)acc;
+                }
+    free(buf);
+    return res;
+}
