@@ -148,7 +148,8 @@ __global__ void __launch_bounds__(k3_max_threads(NO))
         // ---- rows (j0, j1, j2) of column I
         size_t gs = e * prm.NN; // global index of the current run's first double (staged variant)
         double *p = out + e * prm.NN + I;
-        int row_in_run = 0;
+        // staged variant: where this thread's next entry goes (advanced by one row per entry, reset by flush)
+        double *sp = k3_stage + (run % 3u) * prm.run_cap + (int)(gs & 1) + I;
         auto flush = [&](int rows) { // staged variant: ship the `rows` rows staged since the last flush
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(k3_max_threads(NO))
             }
             gs += (size_t)rows * prm.N_in;
             ++run;
-            row_in_run = 0;
+            sp = k3_stage + (run % 3u) * prm.run_cap + (int)(gs & 1) + I;
         };
 #pragma unroll
         for (int j0 = 0; j0 < NO; ++j0)
@@ -205,8 +206,8 @@ __global__ void __launch_bounds__(k3_max_threads(NO))
                                 if (STAGED)
                                 {
                                     if (active)
-                                        k3_stage[(run % 3u) * prm.run_cap + (int)(gs & 1) + row_in_run * prm.N_in + I] = val;
-                                    ++row_in_run;
+                                        *sp = val;
+                                    sp += prm.N_in;
                                 }
                                 else if (active)
                                 {
