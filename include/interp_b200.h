@@ -191,6 +191,13 @@ IB200_API int ib200_ctx_set_lo_kernel(ib200_ctx_t *ctx, int on);
  * (kernels_mass2d_kron.cu: 2 FP64 operations per entry) on/off; default on, $IB200_NO_KRON=1 turns it off: the
  * sum-factorised kernels (DFMA / DMMA stage 2) then serve the same shapes, as they do for every other weight. */
 IB200_API int ib200_ctx_set_kron(ib200_ctx_t *ctx, int on);
+/* ... and for the gradient matrices (compute_gradient_mass_matrix on bilinear quads: the cofactor weight is linear in one
+ * reference coordinate; matching spaces included, with the reference's lower-triangle mirroring).  Default OFF,
+ * $IB200_KRON_GRADIENT=1 turns it on: 50-150x the generic kernel that serves matching spaces otherwise, but a cofactor that
+ * is small against the others (x_xi1 of a nearly axis-aligned quad) is then rounded differently from the reference, which
+ * forms it from O(|x|) products -- agreement 1e-12 of the largest of the four gradient matrices of an element instead of
+ * 1e-12 of each. */
+IB200_API int ib200_ctx_set_kron_gradient(ib200_ctx_t *ctx, int on);
 /* primal L2 projections of bilinear quads by fast diagonalisation (kernels_fastdiag.cu) on/off; default on,
  * $IB200_NO_FASTDIAG=1 turns it off: ib200_l2_project_mapped_batch then assembles and factorises every mass matrix. */
 IB200_API int ib200_ctx_set_fastdiag(ib200_ctx_t *ctx, int on);

@@ -98,6 +98,7 @@ _PROTOTYPES = {
     "ib200_ctx_set_lo_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_fastdiag": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_kron": (C.c_int, [C.c_void_p, C.c_int]),
+    "ib200_ctx_set_kron_gradient": (C.c_int, [C.c_void_p, C.c_int]),
     "ib200_ctx_set_chunk_elements": (C.c_int, [C.c_void_p, C.c_size_t]),
     "ib200_device_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),
     "ib200_device_free": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -188,6 +188,10 @@ class Context:
         """Kronecker-sum mass kernel for bilinear quads on/off (off: the sum-factorised DFMA / DMMA kernels)."""
         check(lib.ib200_ctx_set_kron(self.handle, int(bool(on))))
 
+    def set_kron_gradient(self, on: bool) -> None:
+        """Kronecker-sum kernel also for gradient mass matrices of bilinear quads (default off: see ib200_ctx_set_kron_gradient)."""
+        check(lib.ib200_ctx_set_kron_gradient(self.handle, int(bool(on))))
+
     def set_fastdiag(self, on: bool) -> None:
         """Fast-diagonalisation projection of bilinear quads on/off (off: every mass matrix is assembled and factorised)."""
         check(lib.ib200_ctx_set_fastdiag(self.handle, int(bool(on))))

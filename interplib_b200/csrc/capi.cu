@@ -264,6 +264,8 @@ extern "C" int ib200_ctx_create(int device, ib200_ctx_t **out)
         ctx->fastdiag = std::atoi(env) == 0;
     if (const char *env = std::getenv("IB200_NO_KRON"))
         ctx->kron = std::atoi(env) == 0;
+    if (const char *env = std::getenv("IB200_KRON_GRADIENT"))
+        ctx->kron_gradient = std::atoi(env) != 0;
     IB_CUDA(cudaSetDevice(device));
     IB_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
     if (ctx->prop.major < 10)
@@ -424,6 +426,13 @@ extern "C" int ib200_ctx_set_kron(ib200_ctx_t *ctx, int on)
 {
     IB_TRY(ctx_check(ctx));
     ctx->kron = on != 0;
+    return INTERP_SUCCESS;
+}
+
+extern "C" int ib200_ctx_set_kron_gradient(ib200_ctx_t *ctx, int on)
+{
+    IB_TRY(ctx_check(ctx));
+    ctx->kron_gradient = on != 0;
     return INTERP_SUCCESS;
 }
 
@@ -1296,8 +1305,21 @@ static int mapped_mass_prepare(ib200_ctx *ctx, unsigned ndim, const basis_spec_t
 static int launch_mass2d_bilinear(ib200_ctx *ctx, const LaunchCfg &cfg, const MappedMassOp &m, size_t cnt, const double *geom,
                                   double *out)
 {
-    if (!m.fuse_geometry || m.deriv >= 0)
+    if (!m.fuse_geometry)
         return IB200_ERROR_UNSUPPORTED;
+    if (m.deriv >= 0)
+    {
+        // gradient matrices: the cofactor weight of a bilinear map is linear in one reference coordinate -- the same Kronecker
+        // form; matching spaces take the variant that reproduces the reference's lower-triangle mirroring
+        // Opt-in: the cofactor J_ab of a nearly axis-aligned quad is a small difference of O(|x|) coordinates, which the
+        // reference and this kernel round differently (absolute 1e-16 each); the default path restates the reference's
+        // operation order for J and agrees with it to 1e-12 of every matrix, this one to 1e-12 of the LARGEST of the four.
+        // Small non-matching shapes stay on the sum-factorised kernels, which are faster there.
+        if (!ctx->kron || !ctx->kron_gradient || (!m.symmetric && m.op.N_in < 64))
+            return IB200_ERROR_UNSUPPORTED;
+        return launch_mass2d_kron(ctx, cfg, m.key_kron + ":d" + std::to_string(m.deriv) + std::to_string(m.idx_out), 1, m.basis_out, 1,
+                                  m.basis_in, m.rules, m.geom_basis, cnt, geom, out, m.deriv, m.idx_out, m.symmetric);
+    }
     if (ctx->lo_kernel)
     {
         const int res = launch_mass2d_lo(ctx, cfg, m.key_fused, m.op, m.host, m.match0, m.match1, -1, 2, &m.ghost, -1, cnt, geom, out);

@@ -119,6 +119,7 @@ struct ib200_ctx
     int mma_min_points = 13; // quadrature points per dimension from which the DMMA mass kernel is preferred
     bool lo_kernel = true;   // compile-time specialised low-order mass kernel (IB200_NO_LO_KERNEL=1 disables it)
     bool kron = true;        // Kronecker-sum mass kernel for bilinear quads (IB200_NO_KRON=1: sum-factorised kernels only)
+    bool kron_gradient = false; // ... also for gradient matrices (IB200_KRON_GRADIENT=1; see ib200_ctx_set_kron_gradient)
     bool fastdiag = true;    // primal projections of bilinear quads by fast diagonalisation (IB200_NO_FASTDIAG=1: factorise M)
     size_t chunk_elements = 0;
     // staging (host-pointer calls) and scratch (fused generic path)
@@ -216,7 +217,7 @@ int launch_l2_system_1d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string 
                         double *primal);
 int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, int n_row_groups, const basis_spec_t *rows,
                        int n_col_groups, const basis_spec_t *cols, const integration_spec_t *rules, const basis_spec_t *geom_basis,
-                       size_t E, const double *geom, double *out);
+                       size_t E, const double *geom, double *out, int deriv_in = -1, int idx_out = 0, bool mirror = false);
 int launch_l2proj_fd2d(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, const basis_spec_t *basis,
                        const integration_spec_t *rules, const basis_spec_t *geom_basis, size_t E, const double *fvals,
                        const double *geom, double *out);

@@ -345,3 +345,37 @@ int ib200_tables_pair_moments_k(basis_spec_t bout, basis_spec_t bin, integration
     free(buf);
     return res;
 }
+
+/* As ib200_tables_pair_moments with the DERIVATIVE of the input basis: A[j][i] = sum_q w_q Bout_j(x_q) Bin_i'(x_q),
+ * X[j][i] = sum_q w_q x_q Bout_j(x_q) Bin_i'(x_q) -- the 1-D factors of compute_gradient_mass_matrix along its
+ * differentiated dimension (/root/reference/src/python/mass_matrices.c:341-565). */
+int ib200_tables_pair_moments_deriv(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, double *A, double *X)
+{
+    const unsigned no = bout.order + 1, ni = bin.order + 1, m = rule.order + 1;
+    double *buf = (double *)malloc(sizeof(double) * (2 * (size_t)(no + ni) * m + 2 * m));
+    if (!buf)
+        return INTERP_ERROR_FAILED_ALLOCATION;
+    double *Bo = buf, *Do = Bo + (size_t)no * m, *Bi = Do + (size_t)no * m, *Di = Bi + (size_t)ni * m, *x = Di + (size_t)ni * m,
+           *w = x + m;
+    int res = ib200_tables_rule(rule, x, w, NULL);
+    if (res == INTERP_SUCCESS)
+        res = ib200_tables_basis(bout, rule, Bo, Do);
+    if (res == INTERP_SUCCESS)
+        res = ib200_tables_basis(bin, rule, Bi, Di);
+    if (res == INTERP_SUCCESS)
+        for (unsigned j = 0; j < no; ++j)
+            for (unsigned i = 0; i < ni; ++i)
+            {
+                real a = 0.0L, xx = 0.0L;
+                for (unsigned q = 0; q < m; ++q)
+                {
+                    const real pq = (real)w[q] * ((real)Bo[j * m + q] * (real)Di[i * m + q]);
+                    a += pq;
+                    xx += pq * (real)x[q];
+                }
+                A[j * ni + i] = (double)a;
+                X[j * ni + i] = (double)xx;
+            }
+    free(buf);
+    return res;
+}

@@ -78,6 +78,7 @@ struct FdTabs
     double lam0[N];
     double xi0[M];
     double G[3][4];   // (x_xi0, x_xi1, x_xi0xi1) = G (c00, c01, c10, c11): coefficients of the bilinear coordinate map
+    double Gs[3];     // row sums of G (zero for Lagrange / Bernstein geometry DoFs)
 };
 
 // 1 / d to an ulp or two: hardware seed (about 20 bits) and two Newton steps.  __drcp_rn costs about twice the FP64
@@ -238,12 +239,12 @@ __global__ void __launch_bounds__(kFdWarps * 32)
 #pragma unroll
             for (int k = 0; k < 3; ++k)
             {
-                double ax = 0.0, ay = 0.0;
+                double ax = __dmul_rn(tab.Gs[k], gc[0]), ay = __dmul_rn(tab.Gs[k], gc[4]);
 #pragma unroll
-                for (int c = 0; c < 4; ++c)
+                for (int c = 1; c < 4; ++c) // G c = G (c - c0) + rowsum * c0: exact differences, eps * h instead of eps * |x|
                 {
-                    ax = fma(tab.G[k][c], gc[c], ax);
-                    ay = fma(tab.G[k][c], gc[4 + c], ay);
+                    ax = fma(tab.G[k][c], gc[c] - gc[0], ax);
+                    ay = fma(tab.G[k][c], gc[4 + c] - gc[4], ay);
                 }
                 dx[k] = ax;
                 dy[k] = ay;
@@ -347,6 +348,8 @@ int launch_fd_one(const LaunchCfg &cfg, const FdPlan &plan, size_t E, const doub
     std::memcpy(tab.lam0, plan.lam0.data(), sizeof tab.lam0);
     std::memcpy(tab.xi0, plan.xi0.data(), sizeof tab.xi0);
     std::memcpy(tab.G, plan.G, sizeof tab.G);
+    for (int k = 0; k < 3; ++k)
+        tab.Gs[k] = plan.G[k][0] + plan.G[k][1] + plan.G[k][2] + plan.G[k][3];
     constexpr int EPW = 32 / N, EPB = EPW * kFdWarps, NP = N + (N & 1);
     const size_t n_tiles = (E + EPB - 1) / EPB;
     constexpr int Q = M * M, QP = Q;

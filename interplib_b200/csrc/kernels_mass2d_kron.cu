@@ -38,7 +38,9 @@ struct KronParams
     int n_out0[NG], n_out1[NG]; // basis counts of the row groups
     int N_in;                   // columns = sum over column groups of n_in0 * n_in1
     unsigned long long NN;      // doubles per element matrix
+    int wmode;                  // weight: 0 = det J; 1..4 = det J * Jinv[idx_in][idx_out] for (0,0), (0,1), (1,0), (1,1)
     double G[3][4];             // (x_xi0, x_xi1, x_xi0xi1) = G (c00, c01, c10, c11)
+    double Gs[3];               // row sums of G: zero for the geometry families whose equal DoFs mean a constant
 };
 
 __device__ __forceinline__ double kron_diff_of_products(double a, double b, double c, double d)
@@ -72,16 +74,26 @@ constexpr int kron_max_threads(int NG, int NO)
 //                 profiles/r02h_kron_sweep.jsonl).  The n_out1 rows of one (group, j0) -- a contiguous run of global memory --
 //                 are staged in shared memory (lane = column: conflict-free) with the 16-byte phase of their global address
 //                 and leave as ONE cp.async.bulk shared->global copy; three buffers, one CTA barrier per run.
-template <int NG, int NO, bool STAGED>
+//
+// Gradient matrices (compute_gradient_mass_matrix, mass_matrices.c:341-565): the weight det J * Jinv[idx_in][idx_out] is a
+// cofactor of J -- for a bilinear map linear in ONE reference coordinate, a + b xi0 (idx_in = 0) or a + b xi1 (idx_in = 1) --
+// so the same two operations per entry apply with (alpha, beta, gamma) = (a, b, 0) or (a, 0, b) and the moment tables of the
+// differentiated dimension built from the derivative of the input basis.  MIRROR reproduces the reference's treatment of
+// matching spaces: it evaluates the entries on and below the diagonal only and copies them into the upper triangle
+// (mass_matrices.c:497-560) although a gradient matrix is not symmetric; thread I then also holds the transposed factors
+// and writes f(row I, column J) into the rows J < I of its column.
+template <int NG, int NO, bool STAGED, bool MIRROR>
 __global__ void __launch_bounds__(kron_max_threads(NG, NO))
     mass2d_kron_kernel(const __grid_constant__ KronParams<NG> prm, const double2 *__restrict__ tab0, const double2 *__restrict__ tab1,
-                       size_t E, const double *__restrict__ geom, double *__restrict__ out, unsigned long long *__restrict__ sched)
+                       const double2 *__restrict__ tab0T, const double2 *__restrict__ tab1T, size_t E, const double *__restrict__ geom,
+                       double *__restrict__ out, unsigned long long *__restrict__ sched)
 {
+    static_assert(!MIRROR || NG == 1, "the mirrored variant serves one space");
     const int I = threadIdx.x;
     const bool active = I < prm.N_in;
     const int col = active ? I : 0;
 
-    double a1[NG][NO], x1[NG][NO];
+    double a1[NG][NO], x1[NG][NO], a1T[MIRROR ? NO : 1], x1T[MIRROR ? NO : 1];
 #pragma unroll
     for (int g = 0; g < NG; ++g)
 #pragma unroll
@@ -91,6 +103,16 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
             a1[g][j1] = v.x;
             x1[g][j1] = v.y;
         }
+    if (MIRROR)
+    {
+#pragma unroll
+        for (int j1 = 0; j1 < NO; ++j1)
+        {
+            const double2 v = tab1T[(size_t)col * NO + j1];
+            a1T[MIRROR ? j1 : 0] = v.x;
+            x1T[MIRROR ? j1 : 0] = v.y;
+        }
+    }
 
     __shared__ size_t claim[2];
     size_t e = blockIdx.x, e_next = E;
@@ -121,23 +143,39 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
                 pend = atomicAdd(sched, 1ull);
         }
         // det J = alpha + beta xi0 + gamma xi1 from the corner coordinates [c][i0][i1]
+        // G c = G (c - c0) + (row sum of G) c0: for Lagrange / Bernstein geometry DoFs the row sums vanish (equal DoFs are a
+        // constant, and every row is a derivative), the differences from corner 0 are exact for neighbouring coordinates,
+        // and the coefficients carry eps * h instead of eps * |x|
         double dx[3], dy[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k)
         {
-            double ax = 0.0, ay = 0.0;
+            double ax = __dmul_rn(prm.Gs[k], cc[0]), ay = __dmul_rn(prm.Gs[k], cc[4]);
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
+            for (int c = 1; c < 4; ++c)
             {
-                ax = fma(prm.G[k][c], cc[c], ax);
-                ay = fma(prm.G[k][c], cc[4 + c], ay);
+                ax = fma(prm.G[k][c], cc[c] - cc[0], ax);
+                ay = fma(prm.G[k][c], cc[4 + c] - cc[4], ay);
             }
             dx[k] = ax;
             dy[k] = ay;
         }
-        const double alpha = kron_diff_of_products(dx[0], dy[1], dx[1], dy[0]);
-        const double beta = kron_diff_of_products(dx[0], dy[2], dx[2], dy[0]);
-        const double gamma = kron_diff_of_products(dx[2], dy[1], dx[1], dy[2]);
+        double alpha, beta, gamma;
+        if (prm.wmode == 0)
+        {
+            alpha = kron_diff_of_products(dx[0], dy[1], dx[1], dy[0]);
+            beta = kron_diff_of_products(dx[0], dy[2], dx[2], dy[0]);
+            gamma = kron_diff_of_products(dx[2], dy[1], dx[1], dy[2]);
+        }
+        else
+        {
+            // det J * Jinv = [[y_xi1, -x_xi1], [-y_xi0, x_xi0]]; x_xi0 = dx0 + dx2 xi1, x_xi1 = dx1 + dx2 xi0 (same for y)
+            const int w = prm.wmode;
+            alpha = w == 1 ? dy[1] : (w == 2 ? -dx[1] : (w == 3 ? -dy[0] : dx[0]));
+            const double b = w == 1 ? dy[2] : (w == 2 ? -dx[2] : (w == 3 ? -dy[2] : dx[2]));
+            beta = w <= 2 ? b : 0.0;
+            gamma = w <= 2 ? 0.0 : b;
+        }
 
         if (!STAGED)
         {
@@ -149,24 +187,39 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
                 {
                     const int n0 = prm.n_out0[g], n1 = prm.n_out1[g];
                     const double2 *t0 = tab0 + (size_t)g * NO * prm.N_in + I;
-                    double2 ax_next = t0[0];
+                    const double2 *t0T = MIRROR ? tab0T + I : t0;
+                    double2 ax_next = t0[0], axT_next = t0T[0];
+                    int J = 0; // row (MIRROR: rows above the diagonal of column I take the transposed factors)
 #pragma unroll
                     for (int j0 = 0; j0 < NO; ++j0)
                     {
                         if (j0 < n0)
                         {
                             // the pair of the next j0 is requested before this j0's rows are written (the table has NO rows)
-                            const double2 ax = ax_next;
+                            const double2 ax = ax_next, axT = axT_next;
                             if (j0 + 1 < NO)
+                            {
                                 ax_next = t0[(size_t)(j0 + 1) * prm.N_in];
+                                if (MIRROR)
+                                    axT_next = t0T[(size_t)(j0 + 1) * prm.N_in];
+                            }
                             const double c1 = fma(beta, ax.y, __dmul_rn(alpha, ax.x));
                             const double c2 = __dmul_rn(gamma, ax.x);
+                            const double c1T = fma(beta, axT.y, __dmul_rn(alpha, axT.x));
+                            const double c2T = __dmul_rn(gamma, axT.x);
 #pragma unroll
                             for (int j1 = 0; j1 < NO; ++j1)
                             {
                                 if (j1 < n1)
                                 {
-                                    __stcs(p, fma(c1, a1[g][j1], __dmul_rn(c2, x1[g][j1])));
+                                    double v = fma(c1, a1[g][j1], __dmul_rn(c2, x1[g][j1]));
+                                    if (MIRROR)
+                                    {
+                                        const double vT = fma(c1T, a1T[MIRROR ? j1 : 0], __dmul_rn(c2T, x1T[MIRROR ? j1 : 0]));
+                                        v = J >= I ? v : vT;
+                                        ++J;
+                                    }
+                                    __stcs(p, v);
                                     p += prm.N_in;
                                 }
                             }
@@ -185,17 +238,25 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
             {
                 const int n0 = prm.n_out0[g], n1 = prm.n_out1[g];
                 const double2 *t0 = tab0 + (size_t)g * NO * prm.N_in + col;
-                double2 ax_next = t0[0];
+                const double2 *t0T = MIRROR ? tab0T + col : t0;
+                double2 ax_next = t0[0], axT_next = t0T[0];
+                int J = 0;
 #pragma unroll
                 for (int j0 = 0; j0 < NO; ++j0)
                 {
                     if (j0 < n0)
                     {
-                        const double2 ax = ax_next;
+                        const double2 ax = ax_next, axT = axT_next;
                         if (j0 + 1 < NO)
+                        {
                             ax_next = t0[(size_t)(j0 + 1) * prm.N_in];
+                            if (MIRROR)
+                                axT_next = t0T[(size_t)(j0 + 1) * prm.N_in];
+                        }
                         const double c1 = fma(beta, ax.y, __dmul_rn(alpha, ax.x));
                         const double c2 = __dmul_rn(gamma, ax.x);
+                        const double c1T = fma(beta, axT.y, __dmul_rn(alpha, axT.x));
+                        const double c2T = __dmul_rn(gamma, axT.x);
                         const int par = (int)(gs & 1);
                         double *sm = kron_stage + (run % 3u) * cap + par;
                         if (active)
@@ -206,7 +267,13 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
                             {
                                 if (j1 < n1)
                                 {
-                                    *d = fma(c1, a1[g][j1], __dmul_rn(c2, x1[g][j1]));
+                                    double v = fma(c1, a1[g][j1], __dmul_rn(c2, x1[g][j1]));
+                                    if (MIRROR)
+                                    {
+                                        const double vT = fma(c1T, a1T[MIRROR ? j1 : 0], __dmul_rn(c2T, x1T[MIRROR ? j1 : 0]));
+                                        v = (J + j1) >= I ? v : vT;
+                                    }
+                                    *d = v;
                                     d += prm.N_in;
                                 }
                             }
@@ -236,6 +303,7 @@ __global__ void __launch_bounds__(kron_max_threads(NG, NO))
                         }
                         gs += cnt;
                         ++run;
+                        J += n1;
                     }
                 }
             }
@@ -258,8 +326,10 @@ struct KronPlan
     int NG = 0, NO = 0, N_in = 0, N_out = 0;
     int n_out0[2] = {0, 0}, n_out1[2] = {0, 0};
     double G[3][4] = {};
+    int wmode = 0;
+    bool mirror = false;
     char *d_tab = nullptr;
-    const double2 *d_tab0 = nullptr, *d_tab1 = nullptr;
+    const double2 *d_tab0 = nullptr, *d_tab1 = nullptr, *d_tab0T = nullptr, *d_tab1T = nullptr;
     ~KronPlan()
     {
         if (d_tab)
@@ -267,7 +337,7 @@ struct KronPlan
     }
 };
 
-template <int NG, int NO, bool STAGED>
+template <int NG, int NO, bool STAGED, bool MIRROR>
 int launch_kron(const LaunchCfg &cfg, const KronPlan &plan, size_t E, const double *geom, double *out)
 {
     KronParams<NG> prm;
@@ -279,12 +349,15 @@ int launch_kron(const LaunchCfg &cfg, const KronPlan &plan, size_t E, const doub
     }
     prm.N_in = plan.N_in;
     prm.NN = (unsigned long long)plan.N_out * plan.N_in;
+    prm.wmode = plan.wmode;
     std::memcpy(prm.G, plan.G, sizeof prm.G);
+    for (int k = 0; k < 3; ++k)
+        prm.Gs[k] = plan.G[k][0] + plan.G[k][1] + plan.G[k][2] + plan.G[k][3];
     const int threads = (plan.N_in + 31) / 32 * 32;
     if (threads > kron_max_threads(NG, NO))
         return IB200_ERROR_UNSUPPORTED;
     constexpr bool staged = STAGED;
-    auto kernel = mass2d_kron_kernel<NG, NO, STAGED>;
+    auto kernel = mass2d_kron_kernel<NG, NO, STAGED, MIRROR>;
     const size_t smem_bytes = staged ? sizeof(double) * 3 * (((size_t)NO * plan.N_in + 3) & ~(size_t)1) : 0;
     if (smem_bytes > 224 * 1024)
         return IB200_ERROR_UNSUPPORTED;
@@ -296,7 +369,7 @@ int launch_kron(const LaunchCfg &cfg, const KronPlan &plan, size_t E, const doub
         return IB200_ERROR_UNSUPPORTED;
     const size_t cap = (size_t)cfg.sm_count * per_sm;
     const int grid = (int)std::max<size_t>(1, std::min(E, cap));
-    kernel<<<grid, threads, smem_bytes, cfg.stream>>>(prm, plan.d_tab0, plan.d_tab1, E, geom, out, cfg.sched);
+    kernel<<<grid, threads, smem_bytes, cfg.stream>>>(prm, plan.d_tab0, plan.d_tab1, plan.d_tab0T, plan.d_tab1T, E, geom, out, cfg.sched);
     ++*cfg.launch_counter;
     const cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess)
@@ -326,13 +399,19 @@ int kron_pick(int NG, int need)
 // Row groups `rows[g][2]` (output spaces) x column groups `cols[b][2]` (input spaces) of 2-D tensor-product spaces under
 // `rules[2]`, bilinear geometry `geom_basis[2]` (order 1): out[E][N_out][N_in] with N_out = sum_g n0 n1 of the row groups,
 // N_in likewise; block (g, b) = compute_mass_matrix(cols[b], rows[g], smap) with the determinant weight.
+// deriv_in >= 0: compute_gradient_mass_matrix(cols[0], rows[0], smap, deriv_in, idx_out) instead (one group each way; `key`
+// must tell the variants apart); `mirror`: the spaces match and the reference's lower-triangle mirroring is reproduced.
 // IB200_ERROR_UNSUPPORTED (no error text) outside the envelope.  E == 0 with out == NULL only answers that question.
 int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &key, int n_row_groups, const basis_spec_t *rows,
                        int n_col_groups, const basis_spec_t *cols, const integration_spec_t *rules, const basis_spec_t *geom_basis,
-                       size_t E, const double *geom, double *out)
+                       size_t E, const double *geom, double *out, int deriv_in, int idx_out, bool mirror)
 {
     if (n_row_groups < 1 || n_row_groups > 2 || n_col_groups < 1 || n_col_groups > 2)
         return IB200_ERROR_UNSUPPORTED;
+    if (deriv_in >= 0 && (n_row_groups != 1 || n_col_groups != 1 || deriv_in > 1 || idx_out < 0 || idx_out > 1))
+        return IB200_ERROR_UNSUPPORTED;
+    if (mirror && deriv_in < 0)
+        mirror = false; // plain mass matrices of matching spaces are symmetric as they are
     if (geom_basis[0].order != 1 || geom_basis[1].order != 1)
         return IB200_ERROR_UNSUPPORTED;
     auto it = ctx->plans.find(key);
@@ -356,8 +435,11 @@ int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
             res = ib200_tables_linear_basis(geom_basis[0], a0, s0);
         if (res == INTERP_SUCCESS)
             res = ib200_tables_linear_basis(geom_basis[1], a1, s1);
+        if (mirror && 2 * (4 * NO + 20) * ((N_in + 31) / 32 * 32) > 65536)
+            res = IB200_ERROR_UNSUPPORTED; // the transposed factors double the register tables: does not fit one CTA
         std::vector<double2> tab0((size_t)NG * std::max(NO, 1) * N_in, make_double2(0.0, 0.0)),
-            tab1((size_t)N_in * NG * std::max(NO, 1), make_double2(0.0, 0.0));
+            tab1((size_t)N_in * NG * std::max(NO, 1), make_double2(0.0, 0.0)), tab0T(mirror ? tab0.size() : 0, make_double2(0.0, 0.0)),
+            tab1T(mirror ? tab1.size() : 0, make_double2(0.0, 0.0));
         for (int g = 0; g < NG && res == INTERP_SUCCESS; ++g)
         {
             const int no0 = (int)rows[2 * g].order + 1, no1 = (int)rows[2 * g + 1].order + 1;
@@ -368,9 +450,11 @@ int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
             {
                 const int ni0 = (int)cols[2 * b].order + 1, ni1 = (int)cols[2 * b + 1].order + 1;
                 std::vector<double> A0((size_t)no0 * ni0), X0(A0.size()), A1((size_t)no1 * ni1), X1(A1.size());
-                res = ib200_tables_pair_moments(rows[2 * g], cols[2 * b], rules[0], A0.data(), X0.data());
+                res = (deriv_in == 0 ? ib200_tables_pair_moments_deriv : ib200_tables_pair_moments)(rows[2 * g], cols[2 * b], rules[0],
+                                                                                                      A0.data(), X0.data());
                 if (res == INTERP_SUCCESS)
-                    res = ib200_tables_pair_moments(rows[2 * g + 1], cols[2 * b + 1], rules[1], A1.data(), X1.data());
+                    res = (deriv_in == 1 ? ib200_tables_pair_moments_deriv : ib200_tables_pair_moments)(rows[2 * g + 1], cols[2 * b + 1],
+                                                                                                          rules[1], A1.data(), X1.data());
                 if (res != INTERP_SUCCESS)
                     break;
                 for (int i0 = 0; i0 < ni0; ++i0)
@@ -381,6 +465,13 @@ int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
                             tab0[((size_t)g * NO + j0) * N_in + I] = make_double2(A0[(size_t)j0 * ni0 + i0], X0[(size_t)j0 * ni0 + i0]);
                         for (int j1 = 0; j1 < no1; ++j1)
                             tab1[((size_t)I * NG + g) * NO + j1] = make_double2(A1[(size_t)j1 * ni1 + i1], X1[(size_t)j1 * ni1 + i1]);
+                        if (mirror) // matching spaces (no == ni): factors of f(out = I, in = J), the thread's index on the OUT side
+                        {
+                            for (int j0 = 0; j0 < no0; ++j0)
+                                tab0T[(size_t)j0 * N_in + I] = make_double2(A0[(size_t)i0 * ni0 + j0], X0[(size_t)i0 * ni0 + j0]);
+                            for (int j1 = 0; j1 < no1; ++j1)
+                                tab1T[(size_t)I * NO + j1] = make_double2(A1[(size_t)i1 * ni1 + j1], X1[(size_t)i1 * ni1 + j1]);
+                        }
                     }
                 col0 += ni0 * ni1;
             }
@@ -395,13 +486,19 @@ int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
                     plan->G[2][i0 * 2 + k] = s0[i0] * s1[k];
                 }
             const size_t b0 = tab0.size() * sizeof(double2), b1 = tab1.size() * sizeof(double2);
-            const size_t o1 = (b0 + 255) & ~(size_t)255;
-            if (cudaMalloc((void **)&plan->d_tab, o1 + b1) != cudaSuccess ||
+            const size_t o1 = (b0 + 255) & ~(size_t)255, o2 = o1 + ((b1 + 255) & ~(size_t)255), o3 = o2 + o1;
+            if (cudaMalloc((void **)&plan->d_tab, mirror ? o3 + b1 : o1 + b1) != cudaSuccess ||
                 cudaMemcpy(plan->d_tab, tab0.data(), b0, cudaMemcpyHostToDevice) != cudaSuccess ||
-                cudaMemcpy(plan->d_tab + o1, tab1.data(), b1, cudaMemcpyHostToDevice) != cudaSuccess)
+                cudaMemcpy(plan->d_tab + o1, tab1.data(), b1, cudaMemcpyHostToDevice) != cudaSuccess ||
+                (mirror && (cudaMemcpy(plan->d_tab + o2, tab0T.data(), b0, cudaMemcpyHostToDevice) != cudaSuccess ||
+                            cudaMemcpy(plan->d_tab + o3, tab1T.data(), b1, cudaMemcpyHostToDevice) != cudaSuccess)))
                 return ib200_fail(IB200_ERROR_CUDA, "upload of the Kronecker mass tables failed");
             plan->d_tab0 = (const double2 *)plan->d_tab;
             plan->d_tab1 = (const double2 *)(plan->d_tab + o1);
+            plan->d_tab0T = mirror ? (const double2 *)(plan->d_tab + o2) : plan->d_tab0;
+            plan->d_tab1T = mirror ? (const double2 *)(plan->d_tab + o3) : plan->d_tab1;
+            plan->wmode = deriv_in < 0 ? 0 : 1 + 2 * deriv_in + idx_out;
+            plan->mirror = mirror;
             plan->NG = NG;
             plan->NO = NO;
             plan->N_in = N_in;
@@ -422,10 +519,15 @@ int launch_mass2d_kron(ib200_ctx *ctx, const LaunchCfg &cfg, const std::string &
     if (const char *env = std::getenv("IB200_KRON_STAGED")) // measuring aid: 0 = always direct stores, 1 = always staged
         staged = std::atoi(env) != 0;
 #define IB_KRON(G_, O_) \
-    if (plan.NG == G_ && plan.NO == O_) \
-        return staged ? launch_kron<G_, O_, true>(cfg, plan, E, geom, out) : launch_kron<G_, O_, false>(cfg, plan, E, geom, out);
+    if (plan.NG == G_ && plan.NO == O_ && !plan.mirror) \
+        return staged ? launch_kron<G_, O_, true, false>(cfg, plan, E, geom, out) : launch_kron<G_, O_, false, false>(cfg, plan, E, geom, out);
+#define IB_KRON_M(O_) \
+    if (plan.NG == 1 && plan.NO == O_ && plan.mirror) \
+        return staged ? launch_kron<1, O_, true, true>(cfg, plan, E, geom, out) : launch_kron<1, O_, false, true>(cfg, plan, E, geom, out);
     IB_KRON(1, 3) IB_KRON(1, 5) IB_KRON(1, 7) IB_KRON(1, 9) IB_KRON(1, 11) IB_KRON(1, 13) IB_KRON(1, 17) IB_KRON(1, 21)
     IB_KRON(2, 3) IB_KRON(2, 5) IB_KRON(2, 7) IB_KRON(2, 9) IB_KRON(2, 11)
+    IB_KRON_M(3) IB_KRON_M(5) IB_KRON_M(7) IB_KRON_M(9) IB_KRON_M(11) IB_KRON_M(13) IB_KRON_M(17)
 #undef IB_KRON
+#undef IB_KRON_M
     return IB200_ERROR_UNSUPPORTED;
 }

@@ -44,6 +44,7 @@ struct Kron3Params
     int run_level;         // staged variant: rows per run = 0: whole element, 1: one j0 slab, 2: one (j0, j1) slab
     int run_cap;           // doubles per staging buffer (even, room for the phase double)
     double T[8][8];        // monomial coefficients (1, xi2, xi1, xi1 xi2, xi0, ...) of a coordinate from its 8 geometry DoFs
+    double Ts[8];          // row sums of T (zero for m >= 1 with Lagrange / Bernstein geometry DoFs)
 };
 
 constexpr int k3_max_threads(int NO)
@@ -93,10 +94,12 @@ __global__ void __launch_bounds__(k3_max_threads(NO))
         {
             const int p = threadIdx.x >> 3, m = threadIdx.x & 7;
             const double *c = geom + (e * 3 + p) * 8;
-            double acc = 0.0;
+            // differences from corner 0 are exact for neighbouring coordinates: the coefficients carry eps * h, not eps * |x|
+            const double c0 = __ldg(c);
+            double acc = __dmul_rn(prm.Ts[m], c0); // T c = T (c - c0) + rowsum * c0
 #pragma unroll
-            for (int n = 0; n < 8; ++n)
-                acc = fma(prm.T[m][n], __ldg(c + n), acc);
+            for (int n = 1; n < 8; ++n)
+                acc = fma(prm.T[m][n], __ldg(c + n) - c0, acc);
             xm[p][m] = acc;
         }
         if (threadIdx.x == 0)
@@ -258,6 +261,12 @@ int launch_kron3(const LaunchCfg &cfg, const Kron3Plan &plan, size_t E, const do
     prm.N_in = plan.N_in;
     prm.NN = (unsigned long long)plan.N_out * plan.N_in;
     std::memcpy(prm.T, plan.T, sizeof prm.T);
+    for (int m = 0; m < 8; ++m)
+    {
+        prm.Ts[m] = 0.0;
+        for (int n = 0; n < 8; ++n)
+            prm.Ts[m] += plan.T[m][n];
+    }
     const int threads = std::max(32, (plan.N_in + 31) / 32 * 32);
     if (threads > k3_max_threads(NO))
         return IB200_ERROR_UNSUPPORTED;

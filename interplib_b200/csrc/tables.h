@@ -31,6 +31,7 @@ int ib200_tables_bernstein_from_power(unsigned n, double *c);
 int ib200_tables_fastdiag(basis_spec_t basis, integration_spec_t rule, double *V, double *lambda, double *Vw);
 int ib200_tables_linear_basis(basis_spec_t basis, double a[2], double s[2]);
 int ib200_tables_projector_1d(basis_spec_t basis, integration_spec_t rule, double *P);
+int ib200_tables_pair_moments_deriv(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, double *A, double *X);
 int ib200_tables_pair_moments_k(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, unsigned kmax, double *out);
 int ib200_tables_pair_moments(basis_spec_t bout, basis_spec_t bin, integration_spec_t rule, double *A, double *X);
 
