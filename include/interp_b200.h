@@ -373,6 +373,14 @@ IB200_API int ib200_spd_solve_batch(ib200_ctx_t *ctx, unsigned n, size_t n_eleme
  * positive definite (rule with fewer points than basis functions). */
 IB200_API int ib200_fastdiag_tables(basis_spec_t basis, integration_spec_t rule, double *V, double *lambda, double *Vw);
 
+/* Host tables of the Kronecker-sum mass kernels (csrc/fastdiag.c): out[k][j][i] = sum_q w_q x_q^k Bout_j(x_q) T_i(x_q) for
+ * k = 0..kmax, T = Bin or, with deriv_in != 0, its derivative (kmax <= 1 then).  On an element whose Jacobian determinant is
+ * a polynomial in the reference coordinates -- linear on a bilinear quad, degree 2 per coordinate on a trilinear hexahedron,
+ * constant on a straight segment -- the mass matrix is the Kronecker sum of these tables weighted by the polynomial's
+ * coefficients (kernels_mass2d_kron.cu, kernels_mass3d_kron.cu). */
+IB200_API int ib200_pair_moments(basis_spec_t basis_out, basis_spec_t basis_in, integration_spec_t rule, unsigned kmax,
+                                 int deriv_in, double *out);
+
 /* The whole projection_l2_primal of a batch in one call (python/interplib/integration.py:171-223: dual projection, mass
  * matrix, np.linalg.solve): geometry + f samples in, primal[E][N] out.  Bilinear quads (2-D, order-1 geometry basis, square
  * space) are projected by fast diagonalisation -- no mass matrix exists anywhere (kernels_fastdiag.cu,

@@ -125,6 +125,7 @@ _PROTOTYPES = {
          C.POINTER(C.c_uint), C.c_void_p, C.c_int],
     ),
     "ib200_incidence_matrix": (C.c_int, [BasisSpec, C.c_void_p]),
+    "ib200_pair_moments": (C.c_int, [BasisSpec, BasisSpec, IntegrationSpec, C.c_uint, C.c_int, C.c_void_p]),
     "ib200_fastdiag_tables": (C.c_int, [BasisSpec, IntegrationSpec, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ib200_dof_derivative_batch": (
         C.c_int,

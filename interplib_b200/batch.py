@@ -560,6 +560,15 @@ def incidence_matrix(basis):
     return out
 
 
+def pair_moments(basis_out, basis_in, rule, kmax: int = 1, deriv_in: bool = False) -> np.ndarray:
+    """out[k][j][i] = sum_q w_q x_q^k Bout_j(x_q) Bin_i(x_q) (Bin' with ``deriv_in``): the 1-D tables of the Kronecker-sum mass
+    kernels (ib200_pair_moments)."""
+    out = np.empty((kmax + 1, basis_out[1] + 1, basis_in[1] + 1))
+    check(lib.ib200_pair_moments(basis_specs([basis_out])[0], basis_specs([basis_in])[0], rule_specs([rule])[0], int(kmax),
+                                 int(bool(deriv_in)), out.ctypes.data_as(C.c_void_p)))
+    return out
+
+
 def fastdiag_tables(basis, rule):
     """(V[n][n], lambda[n], Vw[n][m]) of a 1-D basis under a 1-D rule: V^T A V = I, V^T X V = diag(lambda) for the mass
     matrix A and the coordinate-weighted mass matrix X (ib200_fastdiag_tables; the tables of the fast-diagonalisation

@@ -1104,6 +1104,30 @@ extern "C" int ib200_fastdiag_tables(basis_spec_t basis, integration_spec_t rule
     return INTERP_SUCCESS;
 }
 
+extern "C" int ib200_pair_moments(basis_spec_t basis_out, basis_spec_t basis_in, integration_spec_t rule, unsigned kmax, int deriv_in,
+                                  double *out)
+{
+    if (!out)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "out must not be NULL");
+    if (kmax > 8 || (deriv_in && kmax > 1))
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "moments up to x^8 (x^1 with the derivative of the input basis)");
+    int res;
+    if (deriv_in)
+    {
+        const size_t n = (size_t)(basis_out.order + 1) * (basis_in.order + 1);
+        std::vector<double> X(n);
+        res = ib200_tables_pair_moments_deriv(basis_out, basis_in, rule, out, X.data());
+        if (res == INTERP_SUCCESS && kmax >= 1)
+            std::memcpy(out + n, X.data(), n * sizeof(double));
+    }
+    else
+        res = ib200_tables_pair_moments_k(basis_out, basis_in, rule, kmax, out);
+    if (res != INTERP_SUCCESS)
+        return ib200_fail(res, "pair moments: invalid basis (%d, %d) or rule (%d) type", (int)basis_out.type, (int)basis_in.type,
+                          (int)rule.type);
+    return INTERP_SUCCESS;
+}
+
 // ---- N3: incidence / derivative DoFs ------------------------------------------------------------------------
 extern "C" int ib200_incidence_matrix(basis_spec_t basis, double *out)
 {
