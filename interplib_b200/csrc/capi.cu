@@ -1698,7 +1698,9 @@ static int l2_system_impl(ib200_ctx_t *ctx, unsigned ndim, const basis_spec_t *b
                            }
                            IB_TRY(launch_geometry_generic(cfg, gop, n_phys, cnt, g, nullptr, nullptr, nullptr, w, -1, 0));
                            int res = IB200_ERROR_UNSUPPORTED;
-                           if (!cfg.force_generic)
+                           if (!cfg.force_generic && ctx->kron && ndim == 3 && n_phys == 3) // trilinear hexahedra: the same kernel as
+                               res = launch_mass3d_kron(ctx, cfg, key_kron, basis, basis, rules, geom_basis, cnt, g, M); // the separate call
+                           if (res == IB200_ERROR_UNSUPPORTED && !cfg.force_generic)
                                res = launch_mass2d_best(ctx, cfg, key_w, op, host, true, true, -1, 1, nullptr, -1, 0, cnt, w, M);
                            if (res == IB200_ERROR_UNSUPPORTED)
                                res = launch_mass_generic(cfg, op, true, cnt, w, -1, M);
