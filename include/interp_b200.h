@@ -399,6 +399,31 @@ IB200_API int ib200_l2_project_mapped_batch(ib200_ctx_t *ctx, unsigned ndim, con
  * np.sum on the host (python/interplib/integration.py:96-103, domains.py:117). */
 IB200_API int ib200_dot(ib200_ctx_t *ctx, size_t n, const double *a, const double *b, double *out, int where);
 
+/* ib200_dot for callers that must not allocate GPU memory.  (No counterpart in the reference: it has no device code
+ * and no allocator to avoid; this entry point exists for the two kinds of caller named below.)
+ *
+ * Who needs it: (1) a plug-in living inside an application whose own pool allocator has already taken the GPU's
+ * memory -- a raw cudaMalloc then fails, or succeeds behind the pool's back; (2) a solver's time loop on a GPU it
+ * shares with other streams -- cudaMalloc and cudaFree stall the whole device.  ib200_dot needs a context (whose
+ * creation allocates) and takes its block partials and its staging of host vectors from cudaMalloc.  This variant
+ * needs no context and calls no cudaMalloc, cudaFree or other allocating routine, ever: its scratch (592 block
+ * partials, a result slot and room to stage two host vectors) is a fixed array of 16 MiB + 8 KiB compiled into the
+ * library's device code.  Every GPU that loads the library carries that array until the process exits.
+ *
+ * out[0] = sum_i a[i]*b[i], same kernels and reduction tree as ib200_dot, hence the same bits.
+ *   where == IB200_DEVICE: a, b, out are device pointers on the CURRENT device; the work is queued on `cuda_stream`
+ *       (a cudaStream_t; NULL = the default stream) and the call returns without waiting.  Any n.
+ *   where == IB200_HOST:   a, b, out are host pointers; the vectors are staged in the built-in scratch, so
+ *       n <= IB200_DOT_STATIC_MAX_HOST_N -- larger n is refused with IB200_ERROR_UNSUPPORTED and a message naming
+ *       the limit.  Returns after the result has reached out[0] (synchronises `cuda_stream`).
+ * The first call on each GPU looks up the device address of the scratch (once per device, with that device current);
+ * make that first call before any stream capture begins.  The scratch is one array per GPU shared by all callers and
+ * it keeps whatever the last call wrote; each call overwrites everything it later reads, so nothing needs clearing,
+ * but two calls whose kernels overlap on the GPU (different streams, no ordering between them) race on it -- order them
+ * with events or use one stream.  Host threads are serialised by an internal mutex for the duration of the call only. */
+#define IB200_DOT_STATIC_MAX_HOST_N ((size_t)1 << 20)
+IB200_API int ib200_dot_static(size_t n, const double *a, const double *b, double *out, int where, void *cuda_stream);
+
 /* ---- 8(e): collectives over the element partition (NCCL over NVLink / NVSwitch) ------------------------------------ */
 /* The reference is single process and has no communication layer; the element-partitioned path
  * needs two collectives and nothing else: the all-gather of per-rank [E_g][N] DoF / right-hand-side slabs and the

@@ -185,6 +185,7 @@ _PROTOTYPES = {
     ),
     "ib200_spd_solve_batch": (C.c_int, [C.c_void_p, C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]),
     "ib200_dot": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
+    "ib200_dot_static": (C.c_int, [C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "ib200_lagrange_samples": (C.c_int, [C.c_uint, C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint, C.c_void_p]),
     "ib200_gauss_lobatto": (C.c_int, [C.c_uint, C.c_uint, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     "ib200_bernstein_samples": (C.c_int, [C.c_uint, C.c_size_t, C.c_void_p, C.c_void_p]),

@@ -1199,6 +1199,93 @@ int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b,
     return check_launch("dot_final_kernel");
 }
 
+// ---- ib200_dot_static: the same two-pass dot product for callers that must not allocate ---------------------------
+// ib200_dot keeps its 592 block partials (and, for host vectors, a staged copy of a and b) in memory the context
+// obtains from cudaMalloc.  Some users of this library cannot afford that call: a host application whose own pool
+// allocator has already claimed the GPU (a raw cudaMalloc then fails, or punches a hole into the pool's accounting),
+// and a time-stepping loop on a GPU shared with other streams (cudaMalloc / cudaFree synchronise the whole device).
+// For them the scratch below is part of the loaded module: fixed size, present on every GPU that loads the library
+// from module load until the process exits, never allocated or freed by any call.
+//
+// Layout (doubles): [0, 592) block partials | [592] result slot of a host-vector call | [1024, 1024 + MAX) staged a |
+// [1024 + MAX, 1024 + 2 MAX) staged b, MAX = IB200_DOT_STATIC_MAX_HOST_N.  Nothing has to start at zero: every launch
+// overwrites all 592 partials and the result slot before reading them, and the staged vectors are copied in before the
+// kernel reads them, so what the previous call left behind is never observed.
+constexpr size_t kDotStaticMaxN = IB200_DOT_STATIC_MAX_HOST_N;
+constexpr size_t kDotStaticHead = 1024; // partials + result slot, padded so that the staged vectors stay 256-byte aligned
+static_assert(kDotBlocks + 1 <= kDotStaticHead, "partials and result slot must fit the head of the static scratch");
+static __device__ __align__(256) double g_dot_static_scratch[kDotStaticHead + 2 * kDotStaticMaxN];
+
+namespace
+{
+// In host code `g_dot_static_scratch` is only a handle for the runtime, not an address a kernel could use: the device
+// address is looked up once per GPU (with that GPU current) and remembered here.
+constexpr int kDotStaticMaxDevices = 64;
+std::mutex g_dot_static_mutex;
+double *g_dot_static_ptr[kDotStaticMaxDevices] = {};
+
+int dot_static_scratch(double **out)
+{
+    int dev = -1;
+    IB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kDotStaticMaxDevices)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED, "ib200_dot_static: device ordinal %d is outside the %d this table holds", dev,
+                          kDotStaticMaxDevices);
+    if (!g_dot_static_ptr[dev])
+    {
+        void *p = nullptr;
+        IB_CUDA(cudaGetSymbolAddress(&p, g_dot_static_scratch));
+        if (!p)
+            return ib200_fail(IB200_ERROR_CUDA, "ib200_dot_static: the runtime returned no address for the static scratch");
+        g_dot_static_ptr[dev] = (double *)p;
+    }
+    *out = g_dot_static_ptr[dev];
+    return INTERP_SUCCESS;
+}
+} // namespace
+
+extern "C" int ib200_dot_static(size_t n, const double *a, const double *b, double *out, int where, void *cuda_stream)
+{
+    if (!out || (n && (!a || !b)))
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "ib200_dot_static: a/b/out must not be NULL");
+    if (where != IB200_DEVICE && where != IB200_HOST)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "ib200_dot_static: `where` must be IB200_HOST or IB200_DEVICE");
+    if (where == IB200_HOST && n > kDotStaticMaxN)
+        return ib200_fail(IB200_ERROR_UNSUPPORTED,
+                          "ib200_dot_static: %zu host values per vector exceed the %zu the built-in scratch can stage "
+                          "(IB200_DOT_STATIC_MAX_HOST_N); pass device pointers or use ib200_dot",
+                          n, kDotStaticMaxN);
+    // one host thread at a time: the scratch is shared by every caller in the process
+    std::lock_guard<std::mutex> lock(g_dot_static_mutex);
+    double *scratch = nullptr;
+    IB_TRY(dot_static_scratch(&scratch));
+    const cudaStream_t st = (cudaStream_t)cuda_stream;
+    double *partial = scratch, *result = scratch + kDotBlocks;
+    const double *da = a, *db = b;
+    if (where == IB200_HOST)
+    {
+        double *sa = scratch + kDotStaticHead, *sb = sa + kDotStaticMaxN;
+        if (n)
+        {
+            IB_CUDA(cudaMemcpyAsync(sa, a, n * sizeof(double), cudaMemcpyHostToDevice, st));
+            IB_CUDA(cudaMemcpyAsync(sb, b, n * sizeof(double), cudaMemcpyHostToDevice, st));
+        }
+        da = sa;
+        db = sb;
+    }
+    // same kernels, grid and reduction tree as launch_dot: the result is bit-identical to ib200_dot's
+    dot_partial_kernel<<<kDotBlocks, kThreads, 0, st>>>(n, da, db, partial);
+    IB_TRY(check_launch("dot_partial_kernel (static scratch)"));
+    dot_final_kernel<<<1, 32, 0, st>>>(kDotBlocks, partial, where == IB200_HOST ? result : out);
+    IB_TRY(check_launch("dot_final_kernel (static scratch)"));
+    if (where == IB200_HOST)
+    {
+        IB_CUDA(cudaMemcpyAsync(out, result, sizeof(double), cudaMemcpyDeviceToHost, st));
+        IB_CUDA(cudaStreamSynchronize(st));
+    }
+    return INTERP_SUCCESS;
+}
+
 int launch_spd_solve(const LaunchCfg &cfg, unsigned n, size_t E, double *mass, double *rhs)
 {
     if (E == 0 || n == 0)
