@@ -573,22 +573,48 @@ class Runner:
         ms_coll = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True, compute=False), steps)
         comm.check()
 
-        # ---- parity of the collective: a 4096-element slab owned by the LAST rank, recomputed by this rank alone, must equal
-        # the rows the all-gather delivered, bit for bit (GPUTEST boxes have one GPU: this is the driver-visible NCCL check)
+        # ---- parity of the collective, on a step that cannot borrow from earlier ones: every PEER slab of d_all is filled
+        # with NaN first (barrier on both sides, so no push of the checked step can precede the fill), then one whole step
+        # runs, then the head of EVERY rank's slab -- recomputed by this rank alone -- must equal the rows the all-gather
+        # delivered, bit for bit.  A push that never arrived or arrived after the join leaves NaN behind.
+        # (GPUTEST boxes have one GPU: this is the driver-visible check of the collectives.)
+        from interplib_b200._lib import check as _check, lib as _lib
+
+        ctx.synchronize()
+        self.barrier()
+        own_lo, own_hi = part.first * N * 8, (part.first + part.count) * N * 8
+        if own_lo:
+            _check(_lib.ib200_device_memset(ctx.handle, int(d_all), 0xFF, own_lo))
+        if total_elements * N * 8 > own_hi:
+            _check(_lib.ib200_device_memset(ctx.handle, int(d_all) + own_hi, 0xFF, total_elements * N * 8 - own_hi))
+        ctx.synchronize()
+        self.barrier()
         run_all()
         ctx.synchronize()
         proj_sq = float(np.sum(d_norm.download((n_sub,))))  # of a whole step (the collective-only pass re-reduces in place)
-        chk_n = min(4096, part.counts[-1])
-        chk_first = part.offsets[-1]
-        c_g, c_f = upload_inputs(chk_first, chk_n)
-        c_u = ctx.alloc(max(chk_n, 1) * N * 8)
-        ctx.l2_project_mapped(basis, rules, gb, int(c_g), cfg.n_phys, int(c_f), out=int(c_u), where=DEVICE, n_elements=chk_n)
-        ctx.synchronize()
-        mine = c_u.download((chk_n, N))
-        got = d_all.download((chk_n, N), offset_bytes=chk_first * N * 8)
-        parity_local = bool(np.array_equal(mine, got)) and bool(np.isfinite(got).all())
+        parity_local, checked = True, 0
+        for r in range(world):
+            chk_n = min(4096 if r == world - 1 else 512, part.counts[r])
+            if chk_n == 0:
+                continue
+            chk_first = part.offsets[r]
+            c_g, c_f = upload_inputs(chk_first, chk_n)
+            c_u = ctx.alloc(chk_n * N * 8)
+            ctx.l2_project_mapped(basis, rules, gb, int(c_g), cfg.n_phys, int(c_f), out=int(c_u), where=DEVICE, n_elements=chk_n)
+            ctx.synchronize()
+            mine = c_u.download((chk_n, N))
+            got = d_all.download((chk_n, N), offset_bytes=chk_first * N * 8)
+            parity_local = parity_local and bool(np.array_equal(mine, got)) and bool(np.isfinite(got).all())
+            checked += chk_n
+            for b in (c_g, c_f, c_u):
+                b.free()
+        # the LAST row of every peer slab as well: the tail of a push is what a late join would miss
+        for r in range(world):
+            if part.counts[r]:
+                last = d_all.download((1, N), offset_bytes=(part.offsets[r] + part.counts[r] - 1) * N * 8)
+                parity_local = parity_local and bool(np.isfinite(last).all())
         parity = self.max_over_ranks(0.0 if parity_local else 1.0) == 0.0
-        for b in (c_g, c_f, c_u, d_g, d_f, d_b, d_M):
+        for b in (d_g, d_f, d_b, d_M):
             b.free()
 
         # ---- the same 2^24 elements on ONE GPU (rank 0 alone, no collective): the denominator of the strong-scaling efficiency
@@ -652,7 +678,7 @@ class Runner:
             # what NVLink's 900 GB/s into every GPU allows for this job: the gathered DoFs (3.4 GB on every rank) cannot arrive
             # faster than link_bound_ms, however well the transfer hides behind the kernels
             "link_bound_efficiency": ms_single / max(ms_single / world, link_bound_ms) / world,
-            "collective_parity": parity, "projection_norm_sq": proj_sq, "gpu_launches": int(launches) * world,
+            "collective_parity": parity, "collective_parity_check": f"peer slabs NaN-filled before the checked step; {checked} rows over all {world} rank slabs recomputed locally, bit-equal; last row of every slab finite", "projection_norm_sq": proj_sq, "gpu_launches": int(launches) * world,
         }
         return rec
 

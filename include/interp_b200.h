@@ -462,8 +462,13 @@ IB200_API int ib200_comm_join(ib200_comm_t *comm);
  * rank) as gather destination: the ranks exchange CUDA IPC handles and map each other's buffers.  From then on
  * ib200_allgatherv / ib200_allgather_slabs with this `out` push the local slab straight into the peers' buffers -- one
  * copy-engine transfer per peer over NVLink, no SM, no staging, no NCCL kernel -- and the arrival is published by a
- * one-double all-reduce (inside ib200_comm_join for side-stream calls).  IB200_ERROR_UNSUPPORTED, on every rank alike and
- * without error text, when IPC mapping is unavailable or $IB200_NO_P2P_GATHER is set: the NCCL path keeps serving. */
+ * one-double all-reduce (inside ib200_comm_join for side-stream calls).  Ordering contract: every such gather starts with
+ * a one-double all-reduce on the calling stream, so no peer writes into this rank's `out` before this rank's stream has
+ * reached the call -- earlier work queued on that stream (kernels reading the previous gather, own writes into `out`) is
+ * safe, exactly as with an NCCL all-gather; work on OTHER streams of this rank that touches `out` must be ordered by the
+ * caller.  IB200_ERROR_UNSUPPORTED, on every rank alike and without error text, when IPC mapping is unavailable or
+ * $IB200_NO_P2P_GATHER is set: the NCCL path keeps serving.  IB200_ERROR_BAD_ARGUMENT (this rank; UNSUPPORTED on the
+ * others) when `out` is not the base of its allocation. */
 IB200_API int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_t bytes);
 IB200_API int ib200_comm_unregister_gather(ib200_comm_t *comm);
 /* in-place all-reduce(sum) of n doubles in device memory (projection norms) */

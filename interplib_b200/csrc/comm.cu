@@ -6,6 +6,7 @@
 #include <dlfcn.h>
 #include <nccl.h> // types and enums only: every function is resolved with dlsym
 
+#include <cstdint>
 #include <cstdlib>
 #include <mutex>
 #include <vector>
@@ -274,6 +275,9 @@ extern "C" int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *
     ib200_ctx *ctx = comm->ctx;
     std::lock_guard<std::mutex> lock(ctx->mutex);
     cudaStream_t st = ctx->stream;
+    const bool p2p = comm->reg_out && out == comm->reg_out && comm->n_ranks > 1;
+    if (p2p && (offsets[comm->rank] + counts[comm->rank]) * sizeof(double) > comm->reg_bytes)
+        return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "slab exceeds the registered gather buffer");
     if (on_side_stream)
     {
         IB_CUDA(cudaEventRecord(comm->fork, ctx->stream));
@@ -281,16 +285,19 @@ extern "C" int ib200_allgatherv(ib200_comm_t *comm, const double *send, double *
         st = comm->side;
         comm->side_busy = true;
     }
-    if (comm->reg_out && out == comm->reg_out && comm->n_ranks > 1)
+    if (p2p)
     {
         // registered destination: push the local slab straight into every peer's buffer, one copy-engine transfer per peer
         // on its own stream (NVLink / NVSwitch), no SM and no staging involved; arrival is published by the barrier of
         // ib200_comm_join (side stream) or right here (compute stream)
         const size_t bytes = counts[comm->rank] * sizeof(double);
-        if ((offsets[comm->rank] + counts[comm->rank]) * sizeof(double) > comm->reg_bytes)
-            return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "slab exceeds the registered gather buffer");
-        if (!on_side_stream)
-            IB_CUDA(cudaEventRecord(comm->fork, ctx->stream));
+        // entry handshake: a one-double all-reduce on the calling stream before any push.  A peer's push into this
+        // rank's `out` can then only start once THIS rank's stream has reached the call too, i.e. after everything this
+        // rank queued earlier on that stream (kernels still reading the previous gather, its own writes into `out`) --
+        // the stream-ordered entry an NCCL all-gather gives.  The pushes wait for it through `fork`, re-recorded here
+        // (the side stream's wait on the earlier record is already queued and keeps that earlier state).
+        IB_NCCL(comm, g_nccl.AllReduce(comm->flag, comm->flag, 1, ncclDouble, ncclSum, comm->nccl, st));
+        IB_CUDA(cudaEventRecord(comm->fork, st));
         // peers in ring order starting after this rank: at any moment the copies in flight form a permutation, no GPU is
         // the target of all the others at once
         for (int k = 1; k < comm->n_ranks && bytes; ++k)
@@ -344,6 +351,49 @@ extern "C" int ib200_allgather_slabs(ib200_comm_t *comm, const double *local, si
     return ib200_allgatherv(comm, local, out, counts.data(), offsets.data(), 0);
 }
 
+namespace
+{
+// push streams / events and IPC mappings of a (possibly half-finished) registration
+void release_gather_mappings(ib200_comm *comm)
+{
+    for (size_t r = 0; r < comm->push.size(); ++r)
+    {
+        if (comm->push[r])
+        {
+            cudaStreamSynchronize(comm->push[r]);
+            cudaStreamDestroy(comm->push[r]);
+        }
+        if (r < comm->pushed.size() && comm->pushed[r])
+            cudaEventDestroy(comm->pushed[r]);
+    }
+    comm->push.clear();
+    comm->pushed.clear();
+    for (size_t r = 0; r < comm->peer.size(); ++r)
+        if (comm->peer[r])
+            cudaIpcCloseMemHandle(comm->peer[r]);
+    comm->peer.clear();
+    cudaGetLastError();
+}
+
+// true when `p` is the first byte of its device allocation (driver API through dlsym: the library does not link libcuda);
+// when the driver entry point cannot be found the check is skipped
+bool is_allocation_base(const void *p)
+{
+    typedef int (*get_range_fn)(unsigned long long *, size_t *, unsigned long long);
+    static get_range_fn fn = []() -> get_range_fn {
+        void *h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        return h ? (get_range_fn)dlsym(h, "cuMemGetAddressRange_v2") : nullptr;
+    }();
+    if (!fn)
+        return true;
+    unsigned long long base = 0;
+    size_t size = 0;
+    if (fn(&base, &size, (unsigned long long)(uintptr_t)p) != 0)
+        return true;
+    return base == (unsigned long long)(uintptr_t)p;
+}
+} // namespace
+
 // Collective.  Maps every peer's gather destination into this process (CUDA IPC) so that ib200_allgatherv on `out` can push
 // slabs with copy engines.  `out` must be the base of a cudaMalloc allocation (ib200_alloc) of `bytes` bytes, the same size
 // on every rank.  IB200_ERROR_UNSUPPORTED (on every rank alike) when IPC mapping is not available: the caller keeps NCCL.
@@ -377,23 +427,40 @@ extern "C" int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_
     static_assert(sizeof(Slot) % 8 == 0, "slot size");
     std::vector<Slot> slots(n);
     Slot mine{};
+    bool not_base = false;
     mine.bytes = bytes;
     mine.ok = (std::getenv("IB200_NO_P2P_GATHER") == nullptr && cudaIpcGetMemHandle(&mine.handle, out) == cudaSuccess) ? 1 : 0;
     cudaGetLastError();
+    // `out` must be the base of its allocation: cudaIpcOpenMemHandle hands the peers the BASE, so an interior pointer would
+    // make every push land at the wrong offset without any error
+    if (mine.ok && !is_allocation_base(out))
+    {
+        mine.ok = 0;
+        not_base = true;
+    }
+    // from here on every rank must reach the agreeing all-reduce below: local failures only clear `ok`
+    bool ok = true;
     Slot *d_slots = nullptr;
-    IB_CUDA(cudaMalloc((void **)&d_slots, sizeof(Slot) * n));
-    IB_CUDA(cudaMemcpyAsync(d_slots + comm->rank, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream));
+    ok = cudaMalloc((void **)&d_slots, sizeof(Slot) * n) == cudaSuccess;
+    ok = ok && cudaMemcpyAsync(d_slots + comm->rank, &mine, sizeof mine, cudaMemcpyHostToDevice, ctx->stream) == cudaSuccess;
+    if (!ok)
+    {
+        // without device memory this rank cannot even take part in the handle exchange: fail loudly (the peers see the
+        // missing rank through ib200_comm_check / the NCCL watchdog)
+        cudaFree(d_slots);
+        cudaGetLastError();
+        return ib200_fail(IB200_ERROR_CUDA, "ib200_comm_register_gather: no device memory for the handle exchange");
+    }
     const ncclResult_t res = g_nccl.AllGather(d_slots + comm->rank, d_slots, sizeof(Slot), ncclChar, comm->nccl, ctx->stream);
     if (res != ncclSuccess)
     {
         cudaFree(d_slots);
         return nccl_fail(comm, res, "ncclAllGather of the IPC handles");
     }
-    IB_CUDA(cudaMemcpyAsync(slots.data(), d_slots, sizeof(Slot) * n, cudaMemcpyDeviceToHost, ctx->stream));
-    IB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ok = cudaMemcpyAsync(slots.data(), d_slots, sizeof(Slot) * n, cudaMemcpyDeviceToHost, ctx->stream) == cudaSuccess;
+    ok = cudaStreamSynchronize(ctx->stream) == cudaSuccess && ok;
     cudaFree(d_slots);
-    bool ok = true;
-    for (int r = 0; r < n; ++r)
+    for (int r = 0; r < n && ok; ++r)
         ok = ok && slots[r].ok && slots[r].bytes == bytes;
     comm->peer.assign(n, nullptr);
     for (int r = 0; r < n && ok; ++r)
@@ -403,12 +470,24 @@ extern "C" int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_
         void *p = nullptr;
         if (cudaIpcOpenMemHandle(&p, slots[r].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
         {
-            cudaGetLastError();
             ok = false;
             break;
         }
         comm->peer[r] = (double *)p;
     }
+    // the push streams and events are created BEFORE the agreement, so that a failure here is agreed on as well
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    comm->push.assign(n, nullptr);
+    comm->pushed.assign(n, nullptr);
+    for (int r = 0; r < n && ok; ++r)
+    {
+        if (r == comm->rank)
+            continue;
+        ok = cudaStreamCreateWithPriority(&comm->push[r], cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
+             cudaEventCreateWithFlags(&comm->pushed[r], cudaEventDisableTiming) == cudaSuccess;
+    }
+    cudaGetLastError();
     // all ranks or none: agree on the outcome
     double agree = ok ? 0.0 : 1.0;
     IB_CUDA(cudaMemcpyAsync(comm->flag, &agree, sizeof agree, cudaMemcpyHostToDevice, ctx->stream));
@@ -418,23 +497,10 @@ extern "C" int ib200_comm_register_gather(ib200_comm_t *comm, double *out, size_
     IB_CUDA(cudaMemsetAsync(comm->flag, 0, sizeof(double), ctx->stream));
     if (agree != 0.0)
     {
-        for (int r = 0; r < n; ++r)
-            if (comm->peer[r])
-                cudaIpcCloseMemHandle(comm->peer[r]);
-        comm->peer.clear();
-        cudaGetLastError();
+        release_gather_mappings(comm);
+        if (not_base)
+            return ib200_fail(IB200_ERROR_BAD_ARGUMENT, "ib200_comm_register_gather: `out` is not the base of its allocation");
         return IB200_ERROR_UNSUPPORTED;
-    }
-    int prio_lo = 0, prio_hi = 0;
-    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-    comm->push.assign(n, nullptr);
-    comm->pushed.assign(n, nullptr);
-    for (int r = 0; r < n; ++r)
-    {
-        if (r == comm->rank)
-            continue;
-        IB_CUDA(cudaStreamCreateWithPriority(&comm->push[r], cudaStreamNonBlocking, prio_hi));
-        IB_CUDA(cudaEventCreateWithFlags(&comm->pushed[r], cudaEventDisableTiming));
     }
     comm->reg_out = out;
     comm->reg_bytes = bytes;
@@ -446,19 +512,7 @@ extern "C" int ib200_comm_unregister_gather(ib200_comm_t *comm)
     if (!comm || !comm->ctx)
         return INTERP_SUCCESS;
     cudaSetDevice(comm->ctx->device);
-    for (size_t r = 0; r < comm->push.size(); ++r)
-        if (comm->push[r])
-        {
-            cudaStreamSynchronize(comm->push[r]);
-            cudaStreamDestroy(comm->push[r]);
-            cudaEventDestroy(comm->pushed[r]);
-        }
-    comm->push.clear();
-    comm->pushed.clear();
-    for (size_t r = 0; r < comm->peer.size(); ++r)
-        if (comm->peer[r])
-            cudaIpcCloseMemHandle(comm->peer[r]);
-    comm->peer.clear();
+    release_gather_mappings(comm);
     comm->reg_out = nullptr;
     comm->reg_bytes = 0;
     comm->p2p_pending_side = false;

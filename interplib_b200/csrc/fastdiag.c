@@ -20,6 +20,7 @@
  * (and M never has to exist).  This file builds V, lambda and the transformed test functions once per (basis, rule); all
  * arithmetic is in long double so that the tables carry no error of their own at double precision.
  */
+#include <float.h>
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -97,6 +98,9 @@ int ib200_tables_fastdiag(basis_spec_t basis, integration_spec_t rule, double *V
     int res = ib200_tables_rule(rule, x, w, NULL);
     if (res == INTERP_SUCCESS)
         res = ib200_tables_basis(basis, rule, B, D);
+    /* fewer nodes than basis functions: the quadrature mass matrix B W B^T has rank <= m < n whatever the roundoff says */
+    if (res == INTERP_SUCCESS && m < n)
+        res = INTERP_ERROR_BAD_SYSTEM;
     if (res != INTERP_SUCCESS)
         goto done;
     for (unsigned j = 0; j < n; ++j)
@@ -119,7 +123,8 @@ int ib200_tables_fastdiag(basis_spec_t basis, integration_spec_t rule, double *V
         real d = A[j * n + j];
         for (unsigned k = 0; k < j; ++k)
             d -= L[j * n + k] * L[j * n + k];
-        if (!(d > 1e-28L * fabsl(A[j * n + j])) || !(A[j * n + j] > 0.0L))
+        /* a pivot at roundoff level (~ LDBL_EPSILON * A_jj, either sign) means a numerically singular matrix */
+        if (!(A[j * n + j] > 0.0L) || !(d > (real)n * 1e3L * LDBL_EPSILON * A[j * n + j]))
         {
             res = INTERP_ERROR_BAD_SYSTEM;
             goto done;
@@ -256,6 +261,9 @@ int ib200_tables_projector_1d(basis_spec_t basis, integration_spec_t rule, doubl
     int res = ib200_tables_rule(rule, x, w, NULL);
     if (res == INTERP_SUCCESS)
         res = ib200_tables_basis(basis, rule, B, D);
+    /* fewer nodes than basis functions: the quadrature mass matrix B W B^T has rank <= m < n whatever the roundoff says */
+    if (res == INTERP_SUCCESS && m < n)
+        res = INTERP_ERROR_BAD_SYSTEM;
     if (res != INTERP_SUCCESS)
         goto done;
     for (unsigned j = 0; j < n; ++j)
@@ -272,7 +280,8 @@ int ib200_tables_projector_1d(basis_spec_t basis, integration_spec_t rule, doubl
         real d = A[j * n + j];
         for (unsigned k = 0; k < j; ++k)
             d -= L[j * n + k] * L[j * n + k];
-        if (!(d > 1e-28L * fabsl(A[j * n + j])) || !(A[j * n + j] > 0.0L))
+        /* a pivot at roundoff level (~ LDBL_EPSILON * A_jj, either sign) means a numerically singular matrix */
+        if (!(A[j * n + j] > 0.0L) || !(d > (real)n * 1e3L * LDBL_EPSILON * A[j * n + j]))
         {
             res = INTERP_ERROR_BAD_SYSTEM;
             goto done;

@@ -29,9 +29,14 @@ def test_tables_diagonalise_the_pencil(basis, rule):
     assert np.all(np.abs(lam) <= 1.0 + 1e-15)
 
 
-def test_under_integrated_space_is_refused():
+@pytest.mark.parametrize("basis", ["legendre", "bernstein", "lagrange-gauss", GLL, "lagrange-uniform"])
+@pytest.mark.parametrize("rule", [GAUSS, "gauss-lobatto"])
+@pytest.mark.parametrize("n_basis,n_nodes", [(6, 4), (4, 3), (9, 8), (17, 12)])
+def test_under_integrated_space_is_refused(basis, rule, n_basis, n_nodes):
+    """Fewer rule nodes than basis functions -> singular 1-D mass matrix: always INTERP_ERROR_BAD_SYSTEM, never tables built
+    on a roundoff pivot.  (As many nodes as functions is accepted: test_tables_diagonalise_the_pencil has such a pair.)"""
     with pytest.raises(Exception, match="BAD_SYSTEM"):
-        batch.fastdiag_tables(("legendre", 5), (GAUSS, 3))
+        batch.fastdiag_tables((basis, n_basis - 1), (rule, n_nodes - 1))
 
 
 def fastdiag_project(basis, rules, geom_basis, geom, f):
