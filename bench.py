@@ -46,16 +46,20 @@ from interplib_b200 import synthetic as syn  # noqa: E402  (pure NumPy: does not
 # bench line scales it to the elements of its own launch.  Slightly below the algorithmic bytes where the tail of the
 # output is still dirty in the 126 MB L2 when the kernel ends.
 NCU_TRAFFIC_BYTES = {
-    "c2": (1970064432, 1 << 20),   # profiles/r01e_c2_eval2d_full.txt
-    "c5": (5249943208, 1 << 20),   # profiles/r01c_c5_mass2d_lo_full.txt
-    "c4": (43730439000 + 20404992, 1 << 16),  # profiles/r02p_c4_mass2d_kron_staged_full.txt
-    "c3": (43427470000 + 17022720, 1 << 18),  # profiles/r02g_c3_mass2d_kron_full.txt
+    "c2": (1970064432, 1 << 20, "profiles/r01e_c2_eval2d_full.txt (kernel unchanged since)"),
+    "c5": (5249943208, 1 << 20, "profiles/r01c_c5_mass2d_lo_full.txt (kernel unchanged since)"),
+    "c4": (43730439000 + 20404992, 1 << 16, "profiles/r02p_c4_mass2d_kron_staged_full.txt"),
+    "c3": (43427470000 + 17022720, 1 << 18, "profiles/r02g_c3_mass2d_kron_full.txt"),
     "c1": None,
 }
 METRIC = {"c2": "basis_grad_evals_per_s"}
 DEFAULT_ELEMENTS = {"c1": 1024, "c2": 1 << 20, "c3": 1 << 18, "c4": 1 << 16, "c5": 1 << 22}
 # sum-factorised FP64 operation counts per element
 FLOPS_PER_ELEMENT = {"c2": 2 * (2 * 7 * 7 * 8 + 3 * 7 * 8 * 8), "c4": 3.31e6, "c5": 10.9e3, "c3": 0.50e6}
+# what the launched kernel really executes where that differs: the Kronecker-sum kernels of C3 / C4 spend one multiply and
+# one fused multiply-add per matrix entry (3 moment-table terms folded into 2 operations) -- the nominal count
+# above is what a sum-factorised assembly of the same matrices would cost and is reported as "effective" only
+EXECUTED_FLOPS_PER_ELEMENT = {"c4": 2.0 * 289 * 289, "c3": 2.0 * 144 * 144}
 
 
 def peaks():
@@ -263,7 +267,7 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, smax, reasons = [], [], set()
+        sm, smax, power, reasons = [], [], [], set()
         for line in Path(self.path).read_text().splitlines():
             f = [x.strip() for x in line.split(",")]
             if len(f) < 9 or not f[0].isdigit() or int(f[0]) not in gpu_indices:
@@ -273,11 +277,16 @@ class ClockSampler:
                 smax.append(float(f[2]))
             except ValueError:
                 continue
+            try:
+                power.append(float(f[3]))
+            except ValueError:
+                pass
             for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
         os.unlink(self.path)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "sm_min_mhz": min(sm) if sm else None, "power_w": float(np.median(power)) if power else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
@@ -372,7 +381,8 @@ class Runner:
         return n
 
     # ---- one workload: device-resident value + roofline + e2e + CPU baseline ------------------------------------------
-    def measure(self, name: str, steps: int, warmup: int, elements: int | None, sample_clocks: bool, chain_e2e: bool) -> dict:
+    def measure(self, name: str, steps: int, warmup: int, elements: int | None, sample_clocks: bool, chain_e2e: bool,
+                do_e2e: bool = True) -> dict:
         args, ctx, rank, world = self.args, self.ctx, self.rank, self.world
         wl = Workload(name, ctx, rank, elements)
         for _ in range(warmup):
@@ -415,22 +425,29 @@ class Runner:
         kernel_ms = dom_ms_total / max(dom_launches, 1)
         el_per_launch = wl.E * n_dom / max(dom_launches, 1)
         achieved = wl.dominant_bytes_per_elem * el_per_launch / (kernel_ms * 1e-3) / 1e9
-        traffic = NCU_TRAFFIC_BYTES.get(name)
+        traffic = traffic_src = NCU_TRAFFIC_BYTES.get(name)
         if traffic is not None:
+            traffic_src = f"ncu --set full capture {traffic[2]}, {traffic[0]} B per {traffic[1]} elements, scaled to this launch"
             traffic = int(round(traffic[0] * (el_per_launch / traffic[1])))
         roofline = {"bound": "hbm", "achieved": achieved, "peak": self.hbm_peak, "unit": "GB/s", "frac": achieved / self.hbm_peak,
-                    "traffic": traffic, "peak_source": self.peak_src, "kernel": wl.dominant,
+                    "traffic": traffic, "traffic_source": traffic_src, "peak_source": self.peak_src, "kernel": wl.dominant,
                     "algorithmic_bytes_per_element": wl.dominant_bytes_per_elem,
                     "step_algorithmic_bytes_per_element": wl.bytes_per_elem,
                     "step_frac": wl.bytes_per_elem * wl.E / (ms_total_local / steps * 1e-3) / 1e9 / self.hbm_peak,
                     "elements_per_launch": el_per_launch, "kernel_ms": kernel_ms,
                     "kernel_ms_source": "the step's own CUDA-event region" if wl.dominant_is_step else "separate CUDA-event region, dominant kernel alone",
-                    "fp64_flops_per_element": wl.flops_per_elem}
+                    "fp64_effective_flops_per_element": wl.flops_per_elem}
         if wl.flops_per_elem:
             fma, dmma, src = fp64_peak()
-            tf = wl.flops_per_elem * wl.E / (ms_total_local / steps * 1e-3) / 1e12
-            roofline.update({"fp64_tflops": tf, "fp64_peak_tflops": dmma if name == "c4" else fma, "fp64_frac": tf / (dmma if name == "c4" else fma),
-                             "fp64_peak_source": src})
+            step_s = ms_total_local / steps * 1e-3
+            tf = wl.flops_per_elem * wl.E / step_s / 1e12
+            executed = EXECUTED_FLOPS_PER_ELEMENT.get(name, wl.flops_per_elem)
+            tf_x = executed * wl.E / step_s / 1e12
+            # "effective" = the SURVEY's sum-factorised operation count over the step time (what an assembly by quadrature
+            # would have needed); "executed" = what this step's kernels really issue -- equal except for the Kronecker kernels
+            roofline.update({"fp64_effective_tflops": tf, "fp64_effective_frac": tf / fma,
+                             "fp64_executed_flops_per_element": executed, "fp64_executed_tflops": tf_x,
+                             "fp64_executed_frac": tf_x / fma, "fp64_peak_tflops": fma, "fp64_peak_source": src})
 
         # ---- end to end through the host-pointer API (pinned host buffers) ----------------------------------------------
         def time_e2e(step, n):
@@ -442,8 +459,8 @@ class Runner:
             self.barrier()
             return self.max_over_ranks(time.perf_counter() - t0)
 
-        e2e = e2e_full = None
-        if not args.no_e2e:
+        e2e = e2e_full = projection_e2e = None
+        if not args.no_e2e and do_e2e:
             n_e2e = args.e2e_steps or max(3, min(steps, 10))
             note = {"steps": n_e2e, "elements_per_step": wl.E2, "cpu_affinity": self.numa,
                     "timing": "host wall clock around the synchronous C-ABI call with pinned host buffers, max over ranks"}
@@ -457,10 +474,13 @@ class Runner:
             if chain_e2e:
                 wl.e2e_prepare(chain=True)
                 dt = time_e2e(wl.step_e2e_chain, n_e2e)
-                e2e = {"value": wl.E2 * world * n_e2e / dt, "unit": wl.unit, "h2d_bytes_per_step": wl.h2d_bytes(),
-                       "d2h_bytes_per_step": wl.d2h_bytes(chain=True), "ms_per_step": 1e3 * dt / n_e2e, **note,
-                       "path": "chained projection (ib200_l2_project_mapped_batch): geometry + f in, primal DoFs out; the "
-                               "element mass matrices are assembled and consumed on the device and never cross PCIe"}
+                projection_e2e = {
+                    "metric": "l2_projections_per_s", "value": wl.E2 * world * n_e2e / dt, "unit": wl.unit,
+                    "h2d_bytes_per_step": wl.h2d_bytes(), "d2h_bytes_per_step": wl.d2h_bytes(chain=True),
+                    "ms_per_step": 1e3 * dt / n_e2e, **note,
+                    "path": "whole L2 projection in one call (ib200_l2_project_mapped_batch): geometry + f in, primal DoFs out. "
+                            "NOT a mass-matrix number: on these bilinear quads / straight segments the default solver is the "
+                            "fast diagonalisation (1-D projector), so no mass matrix is formed at all"}
                 wl.e2e_release()
 
         # ---- CPU baseline beside it (rank 0, N=1 only) ------------------------------------------------------------------
@@ -479,8 +499,8 @@ class Runner:
                "config": workload_config(name, wl.E), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                "gpu_launches": int(launches) * world, "clocks": clocks,
                "run": {"device": self.info["name"], "sm_count": self.info["sm_count"], "warmup_steps_run": warm_run}}
-        if chain_e2e and e2e_full is not None:
-            rec["e2e_full_outputs"] = e2e_full
+        if projection_e2e is not None:
+            rec["projection_e2e"] = projection_e2e
         wl.free()
         return rec
 
@@ -525,7 +545,8 @@ class Runner:
 
         n_gather = max(1, int(os.environ.get("IB200_BENCH_GATHER_PARTS", "1")))  # pieces the DoF gather is issued in
 
-        def job(d_g, d_f, d_b, d_M, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub):
+        def job(d_g, d_f, d_b, d_M, first: int, count: int, collectives: bool, compute: bool = True, sub: int = sub,
+                gather: bool = True):
             """Mass matrices + L2 projection of `count` elements starting at global element `first` (this rank's block, or all
             of them for the single-rank reference): primal DoFs of the block first (fast diagonalisation), their all-gather
             goes to the communicator's stream, the (M, b) assembly and the norms run meanwhile in n_sub sub-slabs."""
@@ -535,7 +556,7 @@ class Runner:
                 if hi > lo and compute:
                     ctx.l2_project_mapped(basis, rules, gb, int(d_g) + lo * 64, cfg.n_phys, int(d_f) + lo * Q * 8,
                                           out=int(d_all) + (first + lo) * N * 8, where=DEVICE, n_elements=hi - lo)
-                if collectives:
+                if collectives and gather:
                     counts, offsets = part.slab_layout(N, k * gsub, gsub)
                     comm.allgatherv(int(d_all) + (part.first + min(part.count, k * gsub)) * N * 8, d_all, counts, offsets, overlap=True)
             for k in range(n_sub):
@@ -566,11 +587,19 @@ class Runner:
         run_all = lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True)  # noqa: E731
         for _ in range(max(warmup, 3)):
             run_all()
+        sampler = ClockSampler()
+        if rank == 0:
+            sampler.start()
+        for _ in range(20):   # ~0.1-0.4 s of the same job before the timed legs: clocks and power at their loaded state
+            run_all()
         launches0 = ctx.stats()["kernel_launches"]
         ms_step = timed(run_all, steps)
         launches = ctx.stats()["kernel_launches"] - launches0
         ms_compute = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, False), steps)
         ms_coll = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True, compute=False), steps)
+        # the DoF gather is "only on request" -- the same job with the norms all-reduced and the DoFs left sharded
+        ms_reduce_only = timed(lambda: job(d_g, d_f, d_b, d_M, part.first, part.count, True, gather=False), steps)
+        clocks = sampler.stop(set(range(world))) if rank == 0 else None
         comm.check()
 
         # ---- parity of the collective, on a step that cannot borrow from earlier ones: every PEER slab of d_all is filled
@@ -618,14 +647,16 @@ class Runner:
             b.free()
 
         # ---- the same 2^24 elements on ONE GPU (rank 0 alone, no collective): the denominator of the strong-scaling efficiency
-        ms_single = None
+        ms_single = clocks_single = None
         if world > 1:
             if rank == 0:
                 s_g, s_f = upload_inputs(0, total_elements)
                 s_b = ctx.alloc(total_elements * N * 8)
                 s_M = ctx.alloc(total_elements * N * N * 8)
                 one = lambda: job(s_g, s_f, s_b, s_M, 0, total_elements, False, sub=-(-total_elements // n_sub))  # noqa: E731
-                for _ in range(2):
+                sampler1 = ClockSampler()
+                sampler1.start()
+                for _ in range(6):
                     one()
                 ctx.synchronize()
                 k1 = max(3, min(steps, 5))
@@ -634,6 +665,7 @@ class Runner:
                     one()
                 ctx.timer_stop(3)
                 ms_single = ctx.timer_ms(3) / k1
+                clocks_single = sampler1.stop({self.local_rank})
                 for b in (s_g, s_f, s_b, s_M):
                     b.free()
             self.barrier()
@@ -678,6 +710,11 @@ class Runner:
             # what NVLink's 900 GB/s into every GPU allows for this job: the gathered DoFs (3.4 GB on every rank) cannot arrive
             # faster than link_bound_ms, however well the transfer hides behind the kernels
             "link_bound_efficiency": ms_single / max(ms_single / world, link_bound_ms) / world,
+            "reduce_only": {"ms_per_step": ms_reduce_only, "value": total_elements / (ms_reduce_only * 1e-3),
+                            "speedup_vs_single_gpu": ms_single / ms_reduce_only, "efficiency": ms_single / ms_reduce_only / world,
+                            "step": "the same job with the norms all-reduced (NCCL) and the primal DoFs left sharded on their ranks "
+                                    "(SURVEY 8e: the DoF gather is only on request)"},
+            "clocks": clocks, "clocks_single_gpu_leg": clocks_single,
             "collective_parity": parity, "collective_parity_check": f"peer slabs NaN-filled before the checked step; {checked} rows over all {world} rank slabs recomputed locally, bit-equal; last row of every slab finite", "projection_norm_sq": proj_sq, "gpu_launches": int(launches) * world,
         }
         return rec
@@ -705,6 +742,7 @@ def main() -> int:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mass", action="store_true", help="skip the config-5 `mass` record of the default run")
+    ap.add_argument("--no-others", action="store_true", help="skip the config-1/3/4 records of the default run")
     ap.add_argument("--no-strong", action="store_true", help="skip the config-5 strong-scaling record of the default run")
     ap.add_argument("--e2e-steps", type=int, default=0)
     args = ap.parse_args()
@@ -717,9 +755,16 @@ def main() -> int:
     name = args.workload
     head = r.measure(name, args.steps, args.warmup, args.elements or None, sample_clocks=True, chain_e2e=name in ("c5", "c4", "c1"))
     mass = strong = None
+    others = {}
     if name == "c2":
+        if not args.no_others:
+            # BASELINE configs 1, 3, 4: device-resident value + roofline + single-thread CPU baseline (no e2e: 44 GB of
+            # matrices per step over PCIe says nothing the C5 `mass.e2e` does not say already)
+            for other in ("c1", "c3", "c4"):
+                others[other] = r.measure(other, max(5, min(args.steps, 10)), 3, None, sample_clocks=True, chain_e2e=False,
+                                          do_e2e=False)
         if not args.no_mass:
-            mass = r.measure("c5", max(5, min(args.steps, 20)), 3, None, sample_clocks=False, chain_e2e=True)
+            mass = r.measure("c5", max(5, min(args.steps, 20)), 3, None, sample_clocks=True, chain_e2e=True)
         if not args.no_strong:
             strong = r.measure_strong(args.strong_elements, max(5, min(args.steps, 10)), 3)
     if r.rank == 0:
@@ -728,13 +773,17 @@ def main() -> int:
             "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": head["config"], "roofline": head["roofline"],
             "cpu_baseline": head["cpu_baseline"], "e2e": head["e2e"],
-            "gpu_launches": head["gpu_launches"] + (mass["gpu_launches"] if mass else 0) + (strong["gpu_launches"] if strong else 0),
+            "gpu_launches": head["gpu_launches"] + (mass["gpu_launches"] if mass else 0) + (strong["gpu_launches"] if strong else 0)
+            + sum(o["gpu_launches"] for o in others.values()),
             "clocks": head["clocks"], "run": head["run"],
         }
-        if "e2e_full_outputs" in head:
-            line["e2e_full_outputs"] = head["e2e_full_outputs"]
+        if "projection_e2e" in head:
+            line["projection_e2e"] = head["projection_e2e"]
+        for other, rec in others.items():
+            rec["us_per_step"] = 1e3 * rec["ms_per_step"]
+            line[other] = rec
         if mass is not None:
-            line["mass"] = {k: v for k, v in mass.items() if k != "clocks"}
+            line["mass"] = mass
         if strong is not None:
             line["strong"] = strong
         print(json.dumps(line), flush=True)

@@ -153,6 +153,29 @@ def l2_dual(basis, rules, fvals, geom_basis=None, geom_dofs=None, n_phys=0):
     return out
 
 
+def l2_primal(basis, rules, fvals, geom_basis=None, geom_dofs=None, n_phys=0):
+    """The reference's projection_l2_primal (python/interplib/integration.py:171-223: dual DoFs, mass matrix,
+    np.linalg.solve) of tabulated samples, element by element -> primal DoFs out[E][N]."""
+    ip = ref()
+    fs = _fs(ip, basis)
+    isp = _ispace(ip, rules)
+    N = int(np.prod([o + 1 for _, o in basis]))
+    mshape = [o + 1 for _, o in rules]
+    Q = int(np.prod(mshape))
+    f = np.asarray(fvals, dtype=np.float64).reshape(-1, Q)
+    E = f.shape[0]
+    out = np.empty((E, N))
+    if geom_dofs is not None:
+        Ng = int(np.prod([o + 1 for _, o in geom_basis]))
+        g = np.asarray(geom_dofs, dtype=np.float64).reshape(E, n_phys, Ng)
+    for e in range(E):
+        integ = isp if geom_dofs is None else space_map(ip, geom_basis, isp, g[e])[0]
+        fe = f[e].reshape(mshape)
+        primal = ip.projection_l2_primal(lambda *x, fe=fe: fe, fs, integ)
+        out[e] = np.asarray(primal.values).reshape(-1)
+    return out
+
+
 def evaluate_points(basis, x):
     """FunctionSpace.evaluate per element: x[E][ndim][P] -> [E][P][N]"""
     ip = ref()
