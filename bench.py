@@ -590,7 +590,10 @@ class Runner:
         sampler = ClockSampler()
         if rank == 0:
             sampler.start()
-        for _ in range(20):   # ~0.1-0.4 s of the same job before the timed legs: clocks and power at their loaded state
+        # ~1 s of the same job before the timed legs, so that clocks and board power have reached their loaded state (the job
+        # runs into the power cap: 1965 -> ~1790 MHz); the count comes from a max-over-ranks timing, hence equal on every rank
+        n_pre = int(min(400, max(20, 1000.0 / max(timed(run_all, 3), 1e-3))))
+        for _ in range(n_pre):
             run_all()
         launches0 = ctx.stats()["kernel_launches"]
         ms_step = timed(run_all, steps)
@@ -656,9 +659,12 @@ class Runner:
                 one = lambda: job(s_g, s_f, s_b, s_M, 0, total_elements, False, sub=-(-total_elements // n_sub))  # noqa: E731
                 sampler1 = ClockSampler()
                 sampler1.start()
-                for _ in range(6):
-                    one()
+                one()
                 ctx.synchronize()
+                t0 = time.perf_counter()
+                while time.perf_counter() - t0 < 1.0:   # the same ~1 s under load as the multi-rank legs get
+                    one()
+                    ctx.synchronize()
                 k1 = max(3, min(steps, 5))
                 ctx.timer_start(3)
                 for _ in range(k1):
