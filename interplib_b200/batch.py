@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes as C
 import threading
+import weakref
 
 import numpy as np
 
@@ -55,15 +56,32 @@ def _ptr(a):
     return C.c_void_p(int(a))  # raw device / pinned address, DeviceBuffer, DeviceArray
 
 
-class DeviceBuffer:
-    """A device allocation owned by a :class:`Context` (``ib200_device_alloc``)."""
+def _release_device_memory(ctx: "Context", ptr: int) -> None:
+    """Finaliser of an owned :class:`DeviceBuffer`: runs when the last reference is dropped.  A context that is already closed
+    released the memory itself (``Context.close``)."""
+    if ctx.handle and ptr:
+        lib.ib200_device_free(ctx.handle, ptr)
 
-    def __init__(self, ctx: "Context", nbytes: int):
+
+class DeviceBuffer:
+    """A device allocation owned by a :class:`Context` (``ib200_device_alloc``).
+
+    ``owned=False`` (``Context.alloc``): raw memory whose address the caller passes around as an integer; it lives until
+    :meth:`free` or the end of the process.  ``owned=True`` (every buffer behind a :class:`DeviceArray`): the memory is
+    returned when the last Python reference to the buffer goes away -- the arrays that share it (``reshape`` views) each
+    hold one -- or when the context is closed, whichever comes first."""
+
+    def __init__(self, ctx: "Context", nbytes: int, owned: bool = False):
         self.ctx = ctx
         self.nbytes = int(nbytes)
         p = C.c_void_p()
         check(lib.ib200_device_alloc(ctx.handle, self.nbytes, C.byref(p)))
         self.ptr = p.value
+        self._finalizer = None
+        if owned:
+            self._finalizer = weakref.finalize(self, _release_device_memory, ctx, self.ptr)
+            self._finalizer.atexit = False
+            ctx._owned.add(self)
 
     def upload(self, host: np.ndarray) -> "DeviceBuffer":
         host = np.ascontiguousarray(host)
@@ -79,10 +97,14 @@ class DeviceBuffer:
 
     def free(self) -> None:
         if self.ptr:
+            if self._finalizer is not None:
+                self._finalizer.detach()
             check(lib.ib200_device_free(self.ctx.handle, self.ptr))
             self.ptr = None
 
     def __int__(self) -> int:
+        if not self.ptr:
+            raise ValueError("device buffer has been freed")
         return int(self.ptr)
 
 
@@ -90,21 +112,25 @@ class DeviceArray:
     """A float64 array that lives in device memory: what the batched calls return when their inputs are device arrays, so
     that chains (geometry + f -> primal DoFs -> values and gradients at the rule nodes -> ...) never cross PCIe.  Explicit
     transfers only: :meth:`Context.to_device`, :meth:`to_host`.  ``int(a)`` is the device address (usable wherever the
-    ``where=DEVICE`` form of a call takes a raw pointer)."""
+    ``where=DEVICE`` form of a call takes a raw pointer).
+
+    Ownership: the memory belongs to the array and to every ``reshape`` view of it together and is released when the last of
+    them is dropped (intermediates of a chain free themselves) or when the context closes.  :meth:`free` releases it at
+    once for ALL views; using any of them afterwards raises."""
 
     def __init__(self, ctx: "Context", shape, buf: DeviceBuffer | None = None):
         self.ctx = ctx
         self.shape = tuple(int(v) for v in shape)
         self.size = int(np.prod(self.shape, dtype=np.int64))
-        self.buf = buf if buf is not None else DeviceBuffer(ctx, max(self.size, 1) * 8)
+        self.buf = buf if buf is not None else DeviceBuffer(ctx, max(self.size, 1) * 8, owned=True)
         assert self.buf.nbytes >= self.size * 8
 
     @property
     def ptr(self) -> int:
-        return self.buf.ptr
+        return int(self.buf)
 
     def __int__(self) -> int:
-        return int(self.buf.ptr)
+        return int(self.buf)
 
     def reshape(self, *shape) -> "DeviceArray":
         """A view of the same memory with another shape (one ``-1`` allowed)."""
@@ -160,10 +186,13 @@ class Context:
         check(lib.ib200_ctx_create(int(device), C.byref(h)))
         self.handle = h
         self.device = int(device)
+        self._owned = weakref.WeakSet()  # DeviceArray buffers still alive: released with the context
 
     # -- housekeeping ---------------------------------------------------------------------------
     def close(self) -> None:
         if self.handle:
+            for buf in list(self._owned):
+                buf.free()
             check(lib.ib200_ctx_destroy(self.handle))
             self.handle = None
 

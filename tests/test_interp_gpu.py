@@ -279,3 +279,33 @@ def test_device_resident_chain_equals_host_path(ctx):
     assert np.array_equal(one.derivative(1).values, der_d.to_host().values[7])
     for a in (rec_d, der_d.values, dev.values):
         a.free()
+
+
+def test_device_arrays_release_their_memory(ctx):
+    """Results of device-resident calls own their memory: a dropped intermediate gives it back (300 x 1 GiB allocated and
+    dropped in turn would not fit the GPU otherwise), reshape views keep the shared buffer alive until the last one goes,
+    free() releases it for every view at once, and closing a context releases what is still alive."""
+    import gc
+
+    import interplib_b200 as ib
+    from interplib_b200 import batch
+
+    gib = 1 << 27  # doubles
+    for _ in range(300):
+        a = batch.DeviceArray(ctx, (gib,))
+        view = a.reshape(-1, 2)
+        del a
+        assert view.buf.ptr  # the view keeps the buffer alive
+        del view
+    gc.collect()
+    a = ctx.to_device(np.arange(6.0))
+    v = a.reshape(2, 3)
+    a.free()
+    with pytest.raises(ValueError, match="freed"):
+        int(v)
+    own = ib.Context(0)
+    keep = [batch.DeviceArray(own, (gib,)) for _ in range(3)]
+    own.close()
+    assert all(k.buf.ptr is None for k in keep)
+    del keep  # finalisers of buffers whose context is gone must not touch the library
+    gc.collect()
