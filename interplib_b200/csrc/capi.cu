@@ -1229,6 +1229,19 @@ static int launch_mass2d_best(ib200_ctx *ctx, const LaunchCfg &cfg, const std::s
                               bool match0, bool match1, int deriv, int wsrc_kind, const OpHost *geom_host, int widx_in, int widx_out,
                               size_t cnt, const double *wsrc, double *out)
 {
+    if (deriv >= 0 && match0 && match1 && op.ndim == 2 && op.N_in == op.N_out && !getenv("IB200_NO_MIRROR_PASS"))
+    {
+        // Gradient mass matrix on matching spaces: the reference evaluates the lower triangle only and mirrors it
+        // (mass_matrices.c:494-495, :551-560).  The sum-factorised kernels compute the true full matrix -- the pair table of
+        // the dimension without the derivative is still symmetric, which is all they use of "matching" -- and a second,
+        // in-place pass copies the transposed lower triangle over the upper one.  Same Jacobian, same quadrature sums as
+        // the non-matching gradient path, hence the same per-matrix bound against the reference.
+        const int res = launch_mass2d_best(ctx, cfg, key, op, host, match0 && deriv != 0, match1 && deriv != 1, deriv, wsrc_kind,
+                                           geom_host, widx_in, widx_out, cnt, wsrc, out);
+        if (res != INTERP_SUCCESS)
+            return res;
+        return launch_mirror_lower(cfg, cnt, op.N_in, out);
+    }
     if (op.ndim == 2 && op.dim[0].m >= ctx->mma_min_points)
     {
         const int res = launch_mass2d_mma(ctx, cfg, key, op, host, match0, match1, deriv, wsrc_kind, geom_host, widx_in, widx_out,

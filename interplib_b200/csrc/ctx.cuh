@@ -192,6 +192,7 @@ int launch_points_reconstruct(const LaunchCfg &cfg, const PointOp &op, size_t E,
                               unsigned n_fields, const unsigned *masks, double *out);
 int launch_dof_derivative(const LaunchCfg &cfg, int type, int n, size_t pre, size_t post, const double *d_inc, size_t E,
                           const double *in, double *out);
+int launch_mirror_lower(const LaunchCfg &cfg, size_t E, int N, double *out);
 int dot_scratch_doubles();
 int launch_dot(const LaunchCfg &cfg, size_t n, const double *a, const double *b, double *partial, double *out);
 

@@ -1120,6 +1120,63 @@ __global__ void __launch_bounds__(32) dot_final_kernel(int n_partial, const doub
         out[0] = acc;
 }
 
+// ---- lower-triangle mirroring of square per-element matrices, in place: out[e][r][c] = out[e][c][r] for r < c ----
+// The reference fills a matching-space gradient mass matrix from its lower triangle (mass_matrices.c:494-495, :551-560)
+// although that matrix is not symmetric.  The sum-factorised kernels compute the true full matrix; this pass then
+// overwrites the strict upper triangle with the transposed lower one.  One 32 x 32 tile pair per CTA iteration: the
+// lower tile is read row-wise (coalesced), transposed through shared memory and written row-wise into its mirror tile.
+__global__ void __launch_bounds__(256) mirror_lower_kernel(size_t E, int N, double *__restrict__ out)
+{
+    __shared__ double tile[32][33];
+    const int nt = (N + 31) / 32;
+    const size_t pairs = (size_t)nt * (nt + 1) / 2, total = E * pairs;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (size_t w = blockIdx.x; w < total; w += gridDim.x)
+    {
+        const size_t e = w / pairs;
+        const int p = (int)(w % pairs);
+        int tr = 0;
+        while ((tr + 1) * (tr + 2) / 2 <= p)
+            ++tr;
+        const int tc = p - tr * (tr + 1) / 2; // tile (tr, tc) of the lower triangle, tc <= tr
+        double *m = out + e * (size_t)N * N;
+        for (int r = ty; r < 32; r += 8)
+        {
+            const int gr = tr * 32 + r, gc = tc * 32 + tx;
+            if (gr < N && gc < N)
+                tile[r][tx] = m[(size_t)gr * N + gc];
+        }
+        __syncthreads();
+        for (int r = ty; r < 32; r += 8)
+        {
+            const int gr = tc * 32 + r, gc = tr * 32 + tx; // entry of the mirror tile (tc, tr)
+            if (gr < N && gc < N && gr < gc)
+                m[(size_t)gr * N + gc] = tile[tx][r];
+        }
+        __syncthreads();
+    }
+}
+
+// Small matrices (N < 64: at most 32 KB each): one warp per element, every lane copies entries (c, r) -> (r, c) of the
+// strict upper triangle straight in global memory.  The strided reads stay inside the element's few KB, which the L1 serves
+// after the first touch; reads (lower triangle) and writes (upper triangle) never overlap, so no barrier is needed.
+__global__ void __launch_bounds__(256) mirror_lower_small_kernel(size_t E, int N, double *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const size_t warp = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5, n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    const int NN = N * N;
+    for (size_t e = warp; e < E; e += n_warps)
+    {
+        double *m = out + e * (size_t)NN;
+        for (int t = lane; t < NN; t += 32)
+        {
+            const int r = t / N, c = t - r * N;
+            if (r < c)
+                m[t] = m[c * N + r];
+        }
+    }
+}
+
 int grid_for(size_t total_threads, int sm_count)
 {
     const size_t blocks = (total_threads + kThreads - 1) / kThreads;
@@ -1182,6 +1239,24 @@ int launch_l2_generic(const LaunchCfg &cfg, const OpDesc &op, size_t E, const do
     l2_generic_kernel<<<grid_for(E * op.N_in, cfg.sm_count), kThreads, 0, cfg.stream>>>(op, E, fvals, det, out);
     ++*cfg.launch_counter;
     return check_launch("l2_generic_kernel");
+}
+
+int launch_mirror_lower(const LaunchCfg &cfg, size_t E, int N, double *out)
+{
+    if (E == 0 || N < 2)
+        return INTERP_SUCCESS;
+    if (N < 64)
+    {
+        const size_t blocks = (E + 7) / 8, cap = (size_t)cfg.sm_count * 8;
+        mirror_lower_small_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, cfg.stream>>>(E, N, out);
+        ++*cfg.launch_counter;
+        return check_launch("mirror_lower_small_kernel");
+    }
+    const int nt = (N + 31) / 32;
+    const size_t total = E * ((size_t)nt * (nt + 1) / 2), cap = (size_t)cfg.sm_count * 8;
+    mirror_lower_kernel<<<(unsigned)(total < cap ? total : cap), 256, 0, cfg.stream>>>(E, N, out);
+    ++*cfg.launch_counter;
+    return check_launch("mirror_lower_kernel");
 }
 
 int dot_scratch_doubles()

@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """Gradient mass matrices (compute_gradient_mass_matrix) of bilinear quads: Kronecker kernel (opt-in, ib200_ctx_set_kron_gradient)
-against the default path (generic kernel for matching spaces -- the reference's mirroring quirk --, sum-factorised kernels otherwise).
+against the default path (sum-factorised kernels; for matching spaces followed by the in-place mirror pass that reproduces the
+reference's lower-triangle mirroring -- round 2 ran those on the generic kernel).
 Device resident, CUDA events, best of 3.   python tools/bench_gradmass.py"""
 import sys, json; sys.path.insert(0,'/root/repo')
 import numpy as np, interplib_b200 as ib
