@@ -1236,11 +1236,33 @@ static int launch_mass2d_best(ib200_ctx *ctx, const LaunchCfg &cfg, const std::s
         // the dimension without the derivative is still symmetric, which is all they use of "matching" -- and a second,
         // in-place pass copies the transposed lower triangle over the upper one.  Same Jacobian, same quadrature sums as
         // the non-matching gradient path, hence the same per-matrix bound against the reference.
-        const int res = launch_mass2d_best(ctx, cfg, key, op, host, match0 && deriv != 0, match1 && deriv != 1, deriv, wsrc_kind,
-                                           geom_host, widx_in, widx_out, cnt, wsrc, out);
-        if (res != INTERP_SUCCESS)
-            return res;
-        return launch_mirror_lower(cfg, cnt, op.N_in, out);
+        // $IB200_MIRROR_CHUNK_MB > 0 runs both passes chunk by chunk (that many MiB of output each), so that a chunk still sits
+        // in the 126 MB L2 when the mirror pass reads it back.  Measured SLOWER on B200 at every order (p = 4 / 8 / 16 with
+        // 24, 48, 96 MiB chunks: 0.53-0.81 / 0.51-0.72 / 0.29-0.58 of the one-chunk rate, profiles/r03g_chunk_sweep.log --
+        // the ramp and tail of many short persistent launches cost more than the saved DRAM reads), hence off by default and
+        // kept as a knob only.  Chunks are multiples of 1024 elements where that fits (the specialised kernels' tiling),
+        // else of 2 (16-byte alignment of `out` for odd N).
+        static const long chunk_mb = getenv("IB200_MIRROR_CHUNK_MB") ? atol(getenv("IB200_MIRROR_CHUNK_MB")) : 0;
+        const size_t per_elem = sizeof(double) * (size_t)op.N_in * op.N_out;
+        size_t chunk = cnt;
+        if (chunk_mb > 0)
+        {
+            chunk = ((size_t)chunk_mb << 20) / per_elem;
+            chunk = chunk >= 1024 ? (chunk & ~(size_t)1023) : std::max<size_t>(2, chunk & ~(size_t)1);
+        }
+        // element stride of the weight source: fused geometry (kind 2) is bilinear quads in the plane only, geom[e][2][4]
+        const size_t wstride = wsrc_kind == 2 ? 8 : (wsrc_kind == 1 ? (size_t)op.Q : 0);
+        for (size_t done = 0; done < cnt; done += chunk)
+        {
+            const size_t n = std::min(chunk, cnt - done);
+            double *o = out + done * (size_t)op.N_in * op.N_out;
+            const int res = launch_mass2d_best(ctx, cfg, key, op, host, match0 && deriv != 0, match1 && deriv != 1, deriv, wsrc_kind,
+                                               geom_host, widx_in, widx_out, n, wsrc ? wsrc + done * wstride : nullptr, o);
+            if (res != INTERP_SUCCESS)
+                return res; // UNSUPPORTED can only come from the first chunk: nothing has been written then
+            IB_TRY(launch_mirror_lower(cfg, n, op.N_in, o));
+        }
+        return INTERP_SUCCESS;
     }
     if (op.ndim == 2 && op.dim[0].m >= ctx->mma_min_points)
     {
